@@ -1,0 +1,42 @@
+// Internal C++ interface of the tcgen05 GEMM (see gemm.cu).
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/vipt_b200.h"
+
+namespace vipt {
+
+enum GemmEpilogue {
+  EPI_BIAS_F16 = 0,    // out fp16 = acc + bias                      (qkv)
+  EPI_GELU_F16 = 1,    // out fp16 = gelu_erf(acc + bias)            (mlp.fc1)
+  EPI_RELU_F16 = 2,    // out fp16 = relu(acc + bias)                (head conv + folded BN)
+  EPI_BIAS_F32 = 3,    // out fp32 = acc + bias                      (patch embed)
+  EPI_RESID_F32 = 4,   // out fp32 = resid + acc + bias              (attn.proj, mlp.fc2; in place allowed)
+};
+
+struct GemmParams {
+  int M, N, K, G;
+  void* out;
+  int64_t ldc;               // elements
+  int64_t out_group_stride;  // elements added per group g
+  int64_t out_group_col;     // column offset added per group g
+  const float* bias;         // (G, N) or null
+  const float* resid;        // same layout as out (fp32) or null
+};
+
+struct GemmOp {
+  CUtensorMap tmA, tmB;
+  GemmParams p;
+  int bn, epi;
+};
+
+int make_tmap_f16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                  const uint32_t* box);
+int gemm_plan(GemmOp* op, const void* A, int64_t lda, int64_t a_group_stride, const void* W, int64_t ldw,
+              int64_t w_group_stride, int G, int M, int N, int K, int bn, int epi, void* out, int64_t ldc,
+              int64_t out_group_stride, int64_t out_group_col, const float* bias, const float* resid);
+int gemm_launch(const GemmOp& op, int num_sms, cudaStream_t st);
+
+}  // namespace vipt
