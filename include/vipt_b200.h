@@ -31,6 +31,45 @@ const char* vipt_last_error(void);
 int vipt_op_gemm(const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, int bn, int epi,
                  void* out, int64_t ldc, const float* bias, const float* resid, void* stream);
 
+/* Fused crop + zero pad + cv2-exact bilinear resize + /255, mean, std + patch-major store.  Replaces
+ * sample_target (ViPT/lib/train/data/processing_utils.py:14-76) + PreprocessorMM.process
+ * (ViPT/lib/test/tracker/data_utils.py:20-24).  frame_ptrs_dev: device array of B pointers to uint8
+ * (H,W,6) frames; hw_dev (B,2) int H,W; boxes_dev (B,4) double x,y,w,h.  apatch: fp16 (2, B*rows_per_seq, 768),
+ * token rows start at row_base, column = c*256 + ky*16 + kx.  geom_dev (B,4) double: x1, y1, crop_sz, resize_factor. */
+int vipt_op_crop(const void* frame_ptrs_dev, const int* hw_dev, const double* boxes_dev, double factor, int S,
+                 int row_base, int rows_per_seq, void* apatch, double* geom_dev, int* err_dev, int B, void* stream);
+
+/* Fused joint attention over qkv (B*N, 2304) fp16 -> out (B*N, 768) fp16; when ce_prob != NULL also writes the
+ * softmax row of template token 27 over the search keys, per head: ce_prob (B, 12, 256) fp32
+ * (ViPT/lib/models/layers/attn.py:33-59, attn_blocks.py:44-53). */
+int vipt_op_attention(const void* qkv, int B, int N, void* out, float* ce_prob, void* stream);
+
+/* ---- engine: the drop-in for ViPTTrack.initialize/track (ViPT/lib/test/tracker/vipt.py:41-110) and for
+ * build_viptrack(...).forward(template, search, ce_template_mask) (ViPT/lib/models/vipt/ostrack_prompt.py:39-58),
+ * batched over `batch` independent sequences ---- */
+int vipt_engine_create(void** out_engine);
+int vipt_engine_destroy(void* engine);
+/* one call per state_dict entry (fp32, host memory), names exactly as in the reference checkpoint['net']
+ * (vipt.py:21); then finalize packs them (fp16 GEMM operands, BN folded into the head convs, LN folded into
+ * the prompt down-projections) for `batch` concurrent sequences; deep = 1 for vipt_deep, 0 for vipt_shaw. */
+int vipt_engine_set_tensor(void* engine, const char* name, const float* host_data, int64_t numel);
+int vipt_engine_finalize(void* engine, int batch, int deep);
+/* model-level forward on device tensors: template (B,6,128,128) fp32, search (B,6,256,256) fp32.  Outputs are read
+ * with vipt_engine_buffer: score_map, size_map, offset_map, pred_boxes, removed, feat32 (if want_feat32).
+ * debug_stop > 0 stops after that stage (parity tests only). */
+int vipt_engine_forward(void* engine, const float* template_dev, const float* search_dev, int want_feat32,
+                        int debug_stop, void* stream);
+/* initialize(): frame pointers (host array of B device pointers, uint8 HWC 6 channels), hw (B,2), init boxes (B,4). */
+int vipt_engine_init(void* engine, const void* const* frame_dev_ptrs_host, const int* hw_host,
+                     const double* boxes_host, void* stream);
+/* track(): enqueue one step for all B sequences (crop at the current state -> backbone -> head -> state update).
+ * frame_ptrs_dev: DEVICE array of B frame pointers.  No host synchronisation. use_graph: replay a CUDA graph. */
+int vipt_engine_track_enqueue(void* engine, const void* frame_ptrs_dev, int use_graph, void* stream);
+/* copies the latest boxes (B,4) [x,y,w,h] and best scores (B) to host memory and synchronises the stream. */
+int vipt_engine_results(void* engine, double* boxes_host, float* scores_host, void* stream);
+int64_t vipt_engine_info(void* engine, const char* what);
+int vipt_engine_buffer(void* engine, const char* name, void** dev_ptr, int64_t* bytes);
+
 #ifdef __cplusplus
 }
 #endif

@@ -19,6 +19,19 @@ SIGNATURES = {
     "vipt_last_error": (ctypes.c_char_p, []),
     "vipt_op_gemm": (c_int, [c_void_p, c_i64, c_void_p, c_i64, c_int, c_int, c_int, c_int, c_int, c_void_p, c_i64,
                              c_void_p, c_void_p, c_void_p]),
+    "vipt_op_crop": (c_int, [c_void_p, c_void_p, c_void_p, c_double, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                             c_int, c_void_p]),
+    "vipt_op_attention": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "vipt_engine_create": (c_int, [ctypes.POINTER(c_void_p)]),
+    "vipt_engine_destroy": (c_int, [c_void_p]),
+    "vipt_engine_set_tensor": (c_int, [c_void_p, ctypes.c_char_p, c_void_p, c_i64]),
+    "vipt_engine_finalize": (c_int, [c_void_p, c_int, c_int]),
+    "vipt_engine_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]),
+    "vipt_engine_init": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "vipt_engine_track_enqueue": (c_int, [c_void_p, c_void_p, c_int, c_void_p]),
+    "vipt_engine_results": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),
+    "vipt_engine_info": (c_i64, [c_void_p, ctypes.c_char_p]),
+    "vipt_engine_buffer": (c_int, [c_void_p, ctypes.c_char_p, ctypes.POINTER(c_void_p), ctypes.POINTER(c_i64)]),
 }
 
 

@@ -1,8 +1,9 @@
 // extern "C" entry points of libvipt_b200.so (declared in include/vipt_b200.h).
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
-#include "gemm.h"
+#include "engine.h"
 
 static thread_local char g_err[256] = "";
 static void set_err(const char* m) { strncpy(g_err, m, sizeof(g_err) - 1); }
@@ -30,6 +31,100 @@ int vipt_op_gemm(const void* A, int64_t lda, const void* W, int64_t ldw, int M, 
   r = vipt::gemm_launch(op, num_sms(), (cudaStream_t)stream);
   if (r) set_err(cudaGetErrorString(cudaGetLastError()));
   return r;
+}
+
+int vipt_op_crop(const void* frame_ptrs_dev, const int* hw_dev, const double* boxes_dev, double factor, int S,
+                 int row_base, int rows_per_seq, void* apatch, double* geom_dev, int* err_dev, int B, void* stream) {
+  return vipt::launch_crop((const uint8_t* const*)frame_ptrs_dev, hw_dev, boxes_dev, factor, S, row_base, rows_per_seq,
+                           apatch, (int64_t)B * rows_per_seq * 768, geom_dev, err_dev, B, (cudaStream_t)stream);
+}
+
+int vipt_op_attention(const void* qkv, int B, int N, void* out, float* ce_prob, void* stream) {
+  vipt::AttnOp op;
+  int r = vipt::attention_plan(&op, qkv, B, N);
+  if (r) { set_err("attention_plan failed"); return r; }
+  return vipt::attention_launch(op, out, ce_prob, vipt::kCeToken, vipt::kLensT, vipt::kLensX, (cudaStream_t)stream);
+}
+
+// ---------------------------------------------------------------- engine
+int vipt_engine_create(void** out) {
+  if (!out) return VIPT_ERR_ARG;
+  *out = new vipt::Engine();
+  return VIPT_OK;
+}
+int vipt_engine_destroy(void* e) {
+  delete (vipt::Engine*)e;
+  return VIPT_OK;
+}
+int vipt_engine_set_tensor(void* e, const char* name, const float* host_data, int64_t numel) {
+  if (!e || !name || !host_data || numel <= 0) return VIPT_ERR_ARG;
+  return ((vipt::Engine*)e)->set_tensor(name, host_data, numel);
+}
+int vipt_engine_finalize(void* e, int batch, int deep) {
+  if (!e || batch < 1) return VIPT_ERR_ARG;
+  int r = ((vipt::Engine*)e)->finalize(batch, deep != 0);
+  if (r) set_err("finalize failed (missing / mis-sized state_dict entry or CUDA error; see stderr)");
+  return r;
+}
+int vipt_engine_forward(void* e, const float* template_dev, const float* search_dev, int want_feat32, int debug_stop,
+                        void* stream) {
+  if (!e || !template_dev || !search_dev) return VIPT_ERR_ARG;
+  return ((vipt::Engine*)e)->forward_images(template_dev, search_dev, want_feat32 != 0, debug_stop, (cudaStream_t)stream);
+}
+int vipt_engine_init(void* e, const void* const* frame_dev_ptrs_host, const int* hw_host, const double* boxes_host,
+                     void* stream) {
+  if (!e || !frame_dev_ptrs_host || !hw_host || !boxes_host) return VIPT_ERR_ARG;
+  int r = ((vipt::Engine*)e)->init_sequences(frame_dev_ptrs_host, hw_host, boxes_host, (cudaStream_t)stream);
+  if (r == VIPT_ERR_SMALL_BOX) set_err("Too small bounding box.");
+  return r;
+}
+int vipt_engine_track_enqueue(void* e, const void* frame_ptrs_dev, int use_graph, void* stream) {
+  if (!e || !frame_ptrs_dev) return VIPT_ERR_ARG;
+  return ((vipt::Engine*)e)->track_enqueue(frame_ptrs_dev, use_graph != 0, (cudaStream_t)stream);
+}
+int vipt_engine_results(void* ev, double* boxes_host, float* scores_host, void* stream) {
+  vipt::Engine* e = (vipt::Engine*)ev;
+  if (!e || !boxes_host || !scores_host) return VIPT_ERR_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  int herr = 0;
+  if (cudaMemcpyAsync(boxes_host, e->out_boxes, sizeof(double) * 4 * e->B, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+      cudaMemcpyAsync(scores_host, e->out_scores, sizeof(float) * e->B, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+      cudaMemcpyAsync(&herr, e->err, 4, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+      cudaStreamSynchronize(st) != cudaSuccess) {
+    set_err(cudaGetErrorString(cudaGetLastError()));
+    return VIPT_ERR_LAUNCH;
+  }
+  if (herr == VIPT_ERR_SMALL_BOX) set_err("Too small bounding box.");
+  return herr;
+}
+int64_t vipt_engine_info(void* ev, const char* what) {
+  vipt::Engine* e = (vipt::Engine*)ev;
+  if (!e || !what) return -1;
+  if (!strcmp(what, "launches_per_step")) return e->launches_per_step;
+  if (!strcmp(what, "batch")) return e->B;
+  if (!strcmp(what, "final_tokens")) return e->n_tok[vipt::kDepth];
+  if (!strncmp(what, "n_tok_", 6)) { int i = atoi(what + 6); return (i >= 0 && i <= vipt::kDepth) ? e->n_tok[i] : -1; }
+  return -1;
+}
+int vipt_engine_buffer(void* ev, const char* name, void** ptr, int64_t* bytes) {
+  vipt::Engine* e = (vipt::Engine*)ev;
+  if (!e || !name || !ptr || !bytes || !e->finalized) return VIPT_ERR_ARG;
+  const int64_t R = (int64_t)e->B * vipt::kLensFull, RH = (int64_t)e->B * vipt::kLensX;
+  struct Ent { const char* n; void* p; int64_t b; } tab[] = {
+      {"score_map", e->score_map, RH * 4}, {"size_map", e->size_map, 2 * RH * 4}, {"offset_map", e->offset_map, 2 * RH * 4},
+      {"pred_boxes", e->pred_boxes, e->B * 16}, {"removed", e->removed, 3 * RH * 4}, {"ce_score", e->ce_score, 3 * RH * 4},
+      {"feat32", e->feat32, R * 768 * 4}, {"feat16", e->feat16, RH * 768 * 2}, {"x", e->x_final ? e->x_final : e->xA, R * 768 * 4},
+      {"xA", e->xA, R * 768 * 4}, {"xB", e->xB, R * 768 * 4}, {"xn", e->xn, R * 768 * 2}, {"P", e->P, R * 768 * 4},
+      {"XD", e->XD, R * 16 * 4}, {"E", e->E, 2 * R * 768 * 4}, {"qkv", e->qkv, R * 2304 * 2}, {"att", e->att, R * 768 * 2},
+      {"hbuf", e->hbuf, R * 3072 * 2}, {"gi", e->gi_final ? e->gi_final : e->giA, RH * 4}, {"slot_of_pos", e->slot_of_pos, RH * 4},
+      {"h1", e->h1, RH * 768 * 2}, {"h4", e->h4, RH * 96 * 2}, {"state", e->state, e->B * 32}, {"out_boxes", e->out_boxes, e->B * 32},
+      {"out_scores", e->out_scores, e->B * 4}, {"geom_x", e->geom_x, e->B * 32}, {"geom_z", e->geom_z, e->B * 32},
+      {"apatch", e->apatch, 2 * R * 768 * 2}, {"ce_prob", e->ce_prob, (int64_t)e->B * 12 * 256 * 4}, {"perm", e->perm, RH * 4},
+  };
+  for (auto& t : tab)
+    if (!strcmp(t.n, name)) { *ptr = t.p; *bytes = t.b; return VIPT_OK; }
+  set_err("unknown buffer name");
+  return VIPT_ERR_ARG;
 }
 
 }  // extern "C"

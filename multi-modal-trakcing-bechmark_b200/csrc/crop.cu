@@ -1,0 +1,149 @@
+// Fused crop + zero-pad + OpenCV-exact bilinear resize + normalise + patch-major (im2col) store.
+//
+// Replaces, in one HBM-bound kernel, the reference's host-side
+//   sample_target          ViPT/lib/train/data/processing_utils.py:14-76   (cv2 crop/pad/resize)
+//   PreprocessorMM.process ViPT/lib/test/tracker/data_utils.py:20-24       (/255, -mean, /std)
+// and the im2col that Conv2d(k16,s16) (patch_embed.py:28) implies.  Output rows are tokens, columns
+// are c*256 + ky*16 + kx, so the patch embedding is a plain GEMM against proj.weight.view(768,768).
+//
+// Integer arithmetic follows cv::resize INTER_LINEAR for 8-bit images bit-exactly (11-bit fixed-point
+// coefficients, two-stage rounding; exact 2x downscale -> the generic INTER_AREA path that 6-channel
+// images take: round-half-even of the 2x2 mean).  Geometry is evaluated in fp64 like the reference's
+// Python floats (ceil, round-half-even = rint).
+#include "kernels.h"
+#include "sm100_ptx.cuh"
+
+namespace vipt {
+
+__constant__ float c_mean[3] = {0.485f, 0.456f, 0.406f};
+__constant__ float c_std[3] = {0.229f, 0.224f, 0.225f};
+
+struct Taps {
+  int i0, i1;     // source indices in the padded crop (already clipped)
+  int c0, c1;     // 11-bit coefficients
+};
+
+// horizontal taps: fraction zeroed at the borders; vertical: indices clipped, fraction kept
+__device__ __forceinline__ Taps make_taps(int d, int src, double scale, bool horizontal) {
+  float f = (float)__dsub_rn(__dmul_rn((double)d + 0.5, scale), 0.5);   // no FMA contraction: match the CPU
+  int s = (int)floorf(f);
+  f -= (float)s;
+  Taps t;
+  if (horizontal) {
+    if (s < 0) { f = 0.f; s = 0; }
+    if (s >= src - 1) { f = 0.f; s = src - 1; }
+    t.i0 = s;
+    t.i1 = min(s + 1, src - 1);
+  } else {
+    t.i0 = min(max(s, 0), src - 1);
+    t.i1 = min(max(s + 1, 0), src - 1);
+  }
+  t.c0 = __float2int_rn((1.f - f) * 2048.f);
+  t.c1 = __float2int_rn(f * 2048.f);
+  return t;
+}
+
+// grid: (S*S/256, B); one thread per output pixel, all 6 channels.
+__global__ void __launch_bounds__(256)
+crop_kernel(const uint8_t* const* __restrict__ frames, const int* __restrict__ frame_hw,
+            const double* __restrict__ boxes, double factor, int S, int row_base, int rows_per_seq,
+            op_t* __restrict__ apatch, int64_t group_stride, double* __restrict__ geom, int* __restrict__ err) {
+  const int b = blockIdx.y;
+  const int pix = blockIdx.x * 256 + threadIdx.x;
+  const int oy = pix / S, ox = pix % S;
+  const double bx = boxes[b * 4 + 0], by = boxes[b * 4 + 1], bw = boxes[b * 4 + 2], bh = boxes[b * 4 + 3];
+  const double csd = ceil(sqrt(bw * bh) * factor);
+  if (!(csd >= 1.0)) {           // 'Too small bounding box.' (processing_utils.py:34)
+    if (pix == 0) atomicExch(err, VIPT_ERR_SMALL_BOX);
+    return;
+  }
+  const int cs = (int)csd;
+  const int x1 = (int)rint(bx + 0.5 * bw - csd * 0.5);
+  const int y1 = (int)rint(by + 0.5 * bh - csd * 0.5);
+  if (pix == 0 && geom) {
+    geom[b * 4 + 0] = (double)x1; geom[b * 4 + 1] = (double)y1; geom[b * 4 + 2] = csd;
+    geom[b * 4 + 3] = (double)S / csd;       // resize_factor (processing_utils.py:69)
+  }
+  const int H = frame_hw[b * 2 + 0], W = frame_hw[b * 2 + 1];
+  const uint8_t* im = frames[b];
+  // padded-crop pixel (py, px) is image pixel (y1+py, x1+px) when 0 <= Y <= H-2 and 0 <= X <= W-2
+  // (the `+1` in x2_pad / y2_pad drops the last row / column whenever the crop overhangs), else 0.
+  int out[6];
+  auto load6 = [&](int py, int px, int (&v)[6]) {
+    const int Y = y1 + py, X = x1 + px;
+    if (Y >= 0 && Y <= H - 2 && X >= 0 && X <= W - 2) {
+      const uint8_t* p = im + ((size_t)Y * W + X) * 6;
+#pragma unroll
+      for (int c = 0; c < 6; ++c) v[c] = p[c];
+    } else {
+#pragma unroll
+      for (int c = 0; c < 6; ++c) v[c] = 0;
+    }
+  };
+  if (cs == 2 * S) {
+    int a[6], bb[6], c2[6], d[6];
+    load6(2 * oy, 2 * ox, a); load6(2 * oy, 2 * ox + 1, bb); load6(2 * oy + 1, 2 * ox, c2); load6(2 * oy + 1, 2 * ox + 1, d);
+#pragma unroll
+    for (int c = 0; c < 6; ++c) {
+      const int sum = a[c] + bb[c] + c2[c] + d[c];
+      const int q = sum >> 2, r = sum & 3;
+      out[c] = q + ((r == 3) || (r == 2 && (q & 1)));
+    }
+  } else {
+    const double scale = 1.0 / ((double)S / (double)cs);
+    const Taps tx = make_taps(ox, cs, scale, true);
+    const Taps ty = make_taps(oy, cs, scale, false);
+    int p00[6], p01[6], p10[6], p11[6];
+    load6(ty.i0, tx.i0, p00); load6(ty.i0, tx.i1, p01); load6(ty.i1, tx.i0, p10); load6(ty.i1, tx.i1, p11);
+#pragma unroll
+    for (int c = 0; c < 6; ++c) {
+      const int r0 = p00[c] * tx.c0 + p01[c] * tx.c1;
+      const int r1 = p10[c] * tx.c0 + p11[c] * tx.c1;
+      int v = (((ty.c0 * (r0 >> 4)) >> 16) + ((ty.c1 * (r1 >> 4)) >> 16) + 2) >> 2;
+      out[c] = min(max(v, 0), 255);
+    }
+  }
+  const int tps = S / 16;
+  const int token = (oy >> 4) * tps + (ox >> 4);
+  const int col = (oy & 15) * 16 + (ox & 15);
+  const size_t row = (size_t)b * rows_per_seq + row_base + token;
+#pragma unroll
+  for (int c = 0; c < 6; ++c) {
+    const float v = (((float)out[c] / 255.0f) - c_mean[c % 3]) / c_std[c % 3];
+    apatch[(size_t)(c / 3) * group_stride + row * 768 + (c % 3) * 256 + col] = to_op(v);
+  }
+}
+
+// fp32 NCHW (B,6,S,S) -> patch-major fp16 rows (the forward(template, search) entry).
+__global__ void __launch_bounds__(256)
+patchify_kernel(const float* __restrict__ img, int S, int row_base, int rows_per_seq, op_t* __restrict__ apatch,
+                int64_t group_stride) {
+  const int b = blockIdx.y;
+  const int idx = blockIdx.x * 256 + threadIdx.x;   // over 6*S*S
+  const int c = idx / (S * S);
+  const int oy = (idx / S) % S, ox = idx % S;
+  const float v = img[(size_t)b * 6 * S * S + idx];
+  const int tps = S / 16;
+  const int token = (oy >> 4) * tps + (ox >> 4);
+  const int col = (oy & 15) * 16 + (ox & 15);
+  const size_t row = (size_t)b * rows_per_seq + row_base + token;
+  apatch[(size_t)(c / 3) * group_stride + row * 768 + (c % 3) * 256 + col] = to_op(v);
+}
+
+int launch_crop(const uint8_t* const* frames, const int* frame_hw, const double* boxes, double factor, int S,
+                int row_base, int rows_per_seq, void* apatch, int64_t group_stride, double* geom, int* err, int B,
+                cudaStream_t st) {
+  dim3 grid(S * S / 256, B);
+  crop_kernel<<<grid, 256, 0, st>>>(frames, frame_hw, boxes, factor, S, row_base, rows_per_seq,
+                                    reinterpret_cast<op_t*>(apatch), group_stride, geom, err);
+  return cudaGetLastError() == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
+}
+
+int launch_patchify(const float* img, int S, int row_base, int rows_per_seq, void* apatch, int64_t group_stride, int B,
+                    cudaStream_t st) {
+  dim3 grid(6 * S * S / 256, B);
+  patchify_kernel<<<grid, 256, 0, st>>>(img, S, row_base, rows_per_seq, reinterpret_cast<op_t*>(apatch), group_stride);
+  return cudaGetLastError() == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
+}
+
+}  // namespace vipt

@@ -1,0 +1,89 @@
+// Device-resident batched ViPT tracker engine: packed weights, activation buffers sized for a fixed
+// number of concurrent sequences, pre-encoded TMA descriptors, per-sequence state (boxes in fp64).
+#pragma once
+#include <cuda_fp16.h>
+
+#include <map>
+#include <string>
+#include <vector>
+
+#include "kernels.h"
+
+namespace vipt {
+
+constexpr int kDepth = 12;
+constexpr int kLensT = 64;      // template tokens (128/16)^2
+constexpr int kLensX = 256;     // search tokens (256/16)^2
+constexpr int kLensFull = 320;
+constexpr int kEmbed = 768;
+constexpr int kMlp = 3072;
+constexpr int kHeads = 12;
+constexpr int kCeToken = 27;    // CTR_POINT on the 8x8 template grid (ce_utils.py:22-24)
+
+struct LayerW {
+  __half *w_qkv, *w_proj, *w_fc1, *w_fc2;
+  float *b_qkv, *b_proj, *b_fc1, *b_fc2;
+  float *ln1_g, *ln1_b, *ln2_g, *ln2_b;
+};
+struct PromptW {
+  float *wg_a, *wg_d, *sc, *w1, *b1;
+  float smooth;
+};
+
+struct Engine {
+  int B = 0;               // concurrent sequences (fixed)
+  bool deep = true;
+  bool finalized = false;
+  int num_sms = 148;
+  std::map<std::string, std::vector<float>> raw;   // state_dict as uploaded, fp32
+  std::vector<void*> allocs;
+
+  // packed weights
+  __half* w_pe = nullptr; float* b_pe = nullptr;   // (2,768,768), (2,768)
+  float* pos_embed = nullptr;                       // (320,768) z then x
+  LayerW L[kDepth];
+  PromptW PW[kDepth];
+  float *norm_g = nullptr, *norm_b = nullptr;
+  __half *w_c1, *w_c2, *w_c3, *w_c4;               // head convs (BN folded), K order = tap*cin + c
+  float *b_c1, *b_c2, *b_c3, *b_c4, *w5, *b5, *window;
+
+  // CE schedule
+  int n_tok[kDepth + 1];     // tokens entering layer i (attention N); n_tok[12] = final
+  int ce_keep[kDepth];       // 0 if not a CE layer, else number of kept search tokens
+
+  // activations
+  __half *apatch, *xn, *qkv, *att, *hbuf, *feat16, *a_col, *h1, *h2, *h3, *h4;
+  float *E, *xA, *xB, *P, *XD, *ce_prob, *ce_score, *feat32;
+  int *giA, *giB, *perm, *removed, *slot_of_pos, *ident, *err;
+  // outputs / state
+  float *score_map, *size_map, *offset_map, *pred_boxes, *out_scores;
+  double *state, *geom_z, *geom_x, *out_boxes;
+  int* frame_hw;                      // (B,2) H,W
+  const uint8_t** frame_ptrs;         // (B) device array of frame pointers
+
+  // plans (TMA descriptors encoded once)
+  GemmOp g_pe, g_qkv[kDepth], g_proj[kDepth], g_fc1[kDepth], g_fc2[kDepth];
+  GemmOp g_c1, g_c2, g_c3, g_c4;
+  AttnOp a_op[kDepth];
+  int n_mlp[kDepth];         // tokens in layer i's MLP (after CE)
+
+  float* x_final = nullptr;   // residual stream / index list after the last block (debug, forward outputs)
+  int* gi_final = nullptr;
+
+  // CUDA graph of one tracking step
+  cudaGraphExec_t graph_exec = nullptr;
+  long launches_per_step = 0;
+
+  ~Engine();
+  void* dalloc(size_t bytes);
+  int set_tensor(const char* name, const float* data, int64_t numel);
+  int finalize(int batch, bool deep_prompt);
+  int finalize_buffers();
+  int forward_images(const float* template_dev, const float* search_dev, bool want_feat32, int debug_stop,
+                     cudaStream_t st);
+  int run_backbone_head(bool tracking, bool want_feat32, int debug_stop, cudaStream_t st);
+  int init_sequences(const void* const* frames_host_ptrs, const int* hw_host, const double* boxes_host, cudaStream_t st);
+  int track_enqueue(const void* frame_ptrs_dev, bool use_graph, cudaStream_t st);
+};
+
+}  // namespace vipt

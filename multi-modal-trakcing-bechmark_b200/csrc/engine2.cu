@@ -1,0 +1,240 @@
+// Engine part 2: buffers, plans, per-step orchestration.
+#include <math.h>
+#include <stdio.h>
+
+#include "engine.h"
+
+namespace vipt {
+
+#define CK(x)                                                                          \
+  do {                                                                                 \
+    cudaError_t e_ = (x);                                                              \
+    if (e_ != cudaSuccess) {                                                           \
+      fprintf(stderr, "vipt: %s failed: %s (%s:%d)\n", #x, cudaGetErrorString(e_), __FILE__, __LINE__); \
+      return VIPT_ERR_LAUNCH;                                                          \
+    }                                                                                  \
+  } while (0)
+#define RET(x)          \
+  do {                  \
+    int r_ = (x);       \
+    if (r_) return r_;  \
+  } while (0)
+
+int Engine::finalize_buffers() {
+  // candidate-elimination schedule: CE_LOC = [3,6,9], keep ratio 0.7 (attn_blocks.py:40)
+  int ns = kLensX;
+  for (int i = 0; i < kDepth; ++i) {
+    n_tok[i] = kLensT + ns;
+    ce_keep[i] = 0;
+    if (i == 3 || i == 6 || i == 9) {
+      ce_keep[i] = (int)ceil(0.7 * (double)ns);
+      ns = ce_keep[i];
+    }
+    n_mlp[i] = kLensT + ns;
+  }
+  n_tok[kDepth] = kLensT + ns;
+  const size_t R = (size_t)B * kLensFull;
+  const size_t RH = (size_t)B * kLensX;
+#define AL(ptr, type, count)                          \
+  do {                                                \
+    ptr = (type*)dalloc(sizeof(type) * (count));      \
+    if (!ptr) return VIPT_ERR_LAUNCH;                 \
+  } while (0)
+  AL(apatch, __half, 2 * R * 768);
+  AL(E, float, 2 * R * 768);
+  AL(xA, float, R * 768); AL(xB, float, R * 768); AL(P, float, R * 768);
+  AL(XD, float, R * 16);
+  AL(xn, __half, R * 768); AL(qkv, __half, R * 2304); AL(att, __half, R * 768); AL(hbuf, __half, R * 3072);
+  AL(ce_prob, float, (size_t)B * kHeads * kLensX); AL(ce_score, float, 3 * RH);
+  AL(feat16, __half, RH * 768); AL(feat32, float, R * 768);
+  AL(a_col, __half, RH * 6912);        // largest im2col: conv1 (also holds 3 x RH x 2304 etc.)
+  AL(h1, __half, RH * 768); AL(h2, __half, RH * 384); AL(h3, __half, RH * 192); AL(h4, __half, RH * 96);
+  AL(giA, int, RH); AL(giB, int, RH); AL(perm, int, RH); AL(removed, int, 3 * RH); AL(slot_of_pos, int, RH);
+  AL(ident, int, RH); AL(err, int, 1);
+  AL(score_map, float, RH); AL(size_map, float, 2 * RH); AL(offset_map, float, 2 * RH);
+  AL(pred_boxes, float, B * 4); AL(out_scores, float, B);
+  AL(state, double, B * 4); AL(geom_z, double, B * 4); AL(geom_x, double, B * 4); AL(out_boxes, double, B * 4);
+  AL(frame_hw, int, B * 2);
+  frame_ptrs = (const uint8_t**)dalloc(sizeof(void*) * B);
+  if (!frame_ptrs) return VIPT_ERR_LAUNCH;
+#undef AL
+  {
+    std::vector<int> id(RH);
+    for (size_t i = 0; i < RH; ++i) id[i] = (int)(i % kLensX);
+    CK(cudaMemcpy(ident, id.data(), RH * 4, cudaMemcpyHostToDevice));
+    CK(cudaMemset(err, 0, 4));
+    CK(cudaMemset(removed, 0, 3 * RH * 4));
+  }
+  // ---- GEMM / attention plans
+  const int M0 = B * kLensFull;
+  RET(gemm_plan(&g_pe, apatch, 768, (int64_t)M0 * 768, w_pe, 768, 768 * 768, 2, M0, 768, 768, 256, EPI_BIAS_F32, E, 768,
+                (int64_t)M0 * 768, 0, b_pe, nullptr));
+  for (int i = 0; i < kDepth; ++i) {
+    const int Ma = B * n_tok[i], Mm = B * n_mlp[i];
+    RET(gemm_plan(&g_qkv[i], xn, 768, 0, L[i].w_qkv, 768, 0, 1, Ma, 2304, 768, 256, EPI_BIAS_F16, qkv, 2304, 0, 0,
+                  L[i].b_qkv, nullptr));
+    RET(attention_plan(&a_op[i], qkv, B, n_tok[i]));
+    // proj / fc2 write the residual stream in place; which of xA/xB is current is patched at run time
+    RET(gemm_plan(&g_proj[i], att, 768, 0, L[i].w_proj, 768, 0, 1, Ma, 768, 768, 256, EPI_RESID_F32, nullptr, 768, 0, 0,
+                  L[i].b_proj, nullptr));
+    RET(gemm_plan(&g_fc1[i], xn, 768, 0, L[i].w_fc1, 768, 0, 1, Mm, 3072, 768, 256, EPI_GELU_F16, hbuf, 3072, 0, 0,
+                  L[i].b_fc1, nullptr));
+    RET(gemm_plan(&g_fc2[i], hbuf, 3072, 0, L[i].w_fc2, 3072, 0, 1, Mm, 768, 3072, 256, EPI_RESID_F32, nullptr, 768, 0,
+                  0, L[i].b_fc2, nullptr));
+  }
+  const int MH = B * kLensX;
+  RET(gemm_plan(&g_c1, a_col, 6912, 0, w_c1, 6912, 0, 1, MH, 768, 6912, 256, EPI_RELU_F16, h1, 768, 0, 0, b_c1, nullptr));
+  RET(gemm_plan(&g_c2, a_col, 2304, (int64_t)MH * 2304, w_c2, 2304, 128 * 2304, 3, MH, 128, 2304, 128, EPI_RELU_F16, h2,
+                384, 0, 128, b_c2, nullptr));
+  RET(gemm_plan(&g_c3, a_col, 1152, (int64_t)MH * 1152, w_c3, 1152, 64 * 1152, 3, MH, 64, 1152, 64, EPI_RELU_F16, h3, 192,
+                0, 64, b_c3, nullptr));
+  RET(gemm_plan(&g_c4, a_col, 576, (int64_t)MH * 576, w_c4, 576, 32 * 576, 3, MH, 32, 576, 32, EPI_RELU_F16, h4, 96, 0,
+                32, b_c4, nullptr));
+  finalized = true;
+  return VIPT_OK;
+}
+
+// Runs patch-embed .. head on whatever is in `apatch`.  tracking=true also updates the box state.
+// debug_stop > 0 returns after that stage (tests pull intermediate buffers).
+int Engine::run_backbone_head(bool tracking, bool want_feat32, int debug_stop, cudaStream_t st) {
+  long nl = 0;
+  int stage = 0;
+#define STAGE_END()                             \
+  do {                                          \
+    if (debug_stop > 0 && ++stage == debug_stop) return VIPT_OK; \
+  } while (0)
+  const size_t RH = (size_t)B * kLensX;
+  CK(cudaMemcpyAsync(giA, ident, RH * 4, cudaMemcpyDeviceToDevice, st));
+  CK(cudaMemcpyAsync(slot_of_pos, ident, RH * 4, cudaMemcpyDeviceToDevice, st));
+  RET(gemm_launch(g_pe, num_sms, st)); ++nl;
+  STAGE_END();   // 1: E
+  const float* E0 = E;
+  const float* E1 = E + (size_t)B * kLensFull * 768;
+  RET(launch_prompt_a(E0, kLensFull, nullptr, E1, PW[0].wg_a, PW[0].wg_d, PW[0].sc, XD, B, kLensT, kLensFull, st)); ++nl;
+  RET(launch_prompt_b(XD, PW[0].w1, PW[0].b1, PW[0].smooth, P, E0, xA, kLensFull, nullptr, pos_embed, L[0].ln1_g,
+                      L[0].ln1_b, xn, B, kLensT, kLensFull, st)); ++nl;
+  STAGE_END();   // 2: x, xn, P after the input prompt
+  float* x = xA;
+  float* x_other = xB;
+  int* gi = giA;
+  int* gi_other = giB;
+  int ce_idx = 0;
+  for (int i = 0; i < kDepth; ++i) {
+    const int n = n_tok[i];
+    if (i >= 1) {
+      if (deep) {
+        RET(launch_prompt_a(x, n, slot_of_pos, P, PW[i].wg_a, PW[i].wg_d, PW[i].sc, XD, B, kLensT, kLensFull, st)); ++nl;
+        RET(launch_prompt_b(XD, PW[i].w1, PW[i].b1, PW[i].smooth, P, x, x, n, slot_of_pos, nullptr, L[i].ln1_g,
+                            L[i].ln1_b, xn, B, kLensT, kLensFull, st)); ++nl;
+      } else {
+        RET(launch_ln_rows(x, n, nullptr, 0, nullptr, xn, L[i].ln1_g, L[i].ln1_b, B, n, kLensT, st)); ++nl;
+      }
+    }
+    STAGE_END();   // 3 + 7i: x entering block i, xn = LN1(x)
+    RET(gemm_launch(g_qkv[i], num_sms, st)); ++nl;
+    STAGE_END();   // 4 + 7i: qkv
+    RET(attention_launch(a_op[i], att, ce_keep[i] ? ce_prob : nullptr, kCeToken, kLensT, kLensX, st)); ++nl;
+    STAGE_END();   // 5 + 7i: att, ce_prob
+    GemmOp gp = g_proj[i];
+    gp.p.out = x; gp.p.resid = x;
+    RET(gemm_launch(gp, num_sms, st)); ++nl;
+    STAGE_END();   // 6 + 7i: x after attention residual
+    const int nm = n_mlp[i];
+    if (ce_keep[i]) {
+      RET(launch_ce_topk(ce_prob, kHeads, n - kLensT, ce_keep[i], gi, gi_other, perm, removed + (size_t)ce_idx * RH,
+                         slot_of_pos, ce_score + (size_t)ce_idx * RH, kLensX, B, st)); ++nl;
+      RET(launch_ln_rows(x, n, perm, kLensX, x_other, xn, L[i].ln2_g, L[i].ln2_b, B, nm, kLensT, st)); ++nl;
+      float* t = x; x = x_other; x_other = t;
+      int* tg = gi; gi = gi_other; gi_other = tg;
+      ++ce_idx;
+    } else {
+      RET(launch_ln_rows(x, n, nullptr, 0, nullptr, xn, L[i].ln2_g, L[i].ln2_b, B, nm, kLensT, st)); ++nl;
+    }
+    STAGE_END();   // 7 + 7i: x after CE, xn = LN2(x)
+    RET(gemm_launch(g_fc1[i], num_sms, st)); ++nl;
+    STAGE_END();   // 8 + 7i: hbuf
+    GemmOp gf = g_fc2[i];
+    gf.p.out = x; gf.p.resid = x;
+    RET(gemm_launch(gf, num_sms, st)); ++nl;
+    STAGE_END();   // 9 + 7i: x after the block
+  }
+  x_final = x;
+  gi_final = gi;
+  RET(launch_final_norm(x, n_tok[kDepth], slot_of_pos, norm_g, norm_b, feat16, want_feat32 ? feat32 : nullptr, B, kLensT,
+                        kLensFull, st)); ++nl;
+  STAGE_END();   // 87: feat16
+  RET(launch_im2col(feat16, 768, 768, 0, a_col, B, 1, st)); ++nl;
+  RET(gemm_launch(g_c1, num_sms, st)); ++nl;
+  STAGE_END();   // 88: h1
+  RET(launch_im2col(h1, 768, 256, 256, a_col, B, 3, st)); ++nl;
+  RET(gemm_launch(g_c2, num_sms, st)); ++nl;
+  RET(launch_im2col(h2, 384, 128, 128, a_col, B, 3, st)); ++nl;
+  RET(gemm_launch(g_c3, num_sms, st)); ++nl;
+  RET(launch_im2col(h3, 192, 64, 64, a_col, B, 3, st)); ++nl;
+  RET(gemm_launch(g_c4, num_sms, st)); ++nl;
+  STAGE_END();   // 89: h4
+  RET(launch_head_final(h4, w5, b5, window, score_map, size_map, offset_map, pred_boxes, tracking ? state : nullptr,
+                        geom_x, frame_hw, out_boxes, out_scores, B, st)); ++nl;
+  launches_per_step = nl;
+#undef STAGE_END
+  return VIPT_OK;
+}
+
+int Engine::forward_images(const float* template_dev, const float* search_dev, bool want_feat32, int debug_stop,
+                           cudaStream_t st) {
+  if (!finalized) return VIPT_ERR_STATE;
+  const int64_t gs = (int64_t)B * kLensFull * 768;
+  RET(launch_patchify(template_dev, 128, 0, kLensFull, apatch, gs, B, st));
+  RET(launch_patchify(search_dev, 256, kLensT, kLensFull, apatch, gs, B, st));
+  return run_backbone_head(false, want_feat32, debug_stop, st);
+}
+
+int Engine::init_sequences(const void* const* frames_host_ptrs, const int* hw_host, const double* boxes_host,
+                           cudaStream_t st) {
+  if (!finalized) return VIPT_ERR_STATE;
+  CK(cudaMemcpyAsync(frame_ptrs, frames_host_ptrs, sizeof(void*) * B, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(frame_hw, hw_host, sizeof(int) * 2 * B, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(state, boxes_host, sizeof(double) * 4 * B, cudaMemcpyHostToDevice, st));
+  CK(cudaMemsetAsync(err, 0, 4, st));
+  const int64_t gs = (int64_t)B * kLensFull * 768;
+  // template: factor 2.0 -> 128 x 128 (vipt.py:43-48); the crop is kept as the resident patch rows 0..63
+  RET(launch_crop(frame_ptrs, frame_hw, state, 2.0, 128, 0, kLensFull, apatch, gs, geom_z, err, B, st));
+  int herr = 0;
+  CK(cudaMemcpyAsync(&herr, err, 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return herr;
+}
+
+int Engine::track_enqueue(const void* frame_ptrs_dev, bool use_graph, cudaStream_t st) {
+  if (!finalized) return VIPT_ERR_STATE;
+  CK(cudaMemcpyAsync(frame_ptrs, frame_ptrs_dev, sizeof(void*) * B, cudaMemcpyDeviceToDevice, st));
+  if (use_graph && graph_exec) {
+    CK(cudaGraphLaunch(graph_exec, st));
+    return VIPT_OK;
+  }
+  const int64_t gs = (int64_t)B * kLensFull * 768;
+  auto body = [&](cudaStream_t s) -> int {
+    // search: factor 4.0 -> 256 x 256 around the current state (vipt.py:67-69)
+    RET(launch_crop(frame_ptrs, frame_hw, state, 4.0, 256, kLensT, kLensFull, apatch, gs, geom_x, err, B, s));
+    return run_backbone_head(true, false, 0, s);
+  };
+  if (!use_graph) {
+    int r = body(st);
+    launches_per_step += 1;
+    return r;
+  }
+  // first graph request: capture one step, instantiate, launch
+  cudaGraph_t graph = nullptr;
+  CK(cudaStreamBeginCapture(st, cudaStreamCaptureModeRelaxed));
+  int r = body(st);
+  cudaError_t ce = cudaStreamEndCapture(st, &graph);
+  if (r) { if (graph) cudaGraphDestroy(graph); return r; }
+  CK(ce);
+  launches_per_step += 1;
+  CK(cudaGraphInstantiate(&graph_exec, graph, 0));
+  cudaGraphDestroy(graph);
+  CK(cudaGraphLaunch(graph_exec, st));
+  return VIPT_OK;
+}
+
+}  // namespace vipt

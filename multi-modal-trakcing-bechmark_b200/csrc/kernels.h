@@ -1,0 +1,42 @@
+// Internal launchers of the non-GEMM kernels (crop.cu, tokens.cu, tokens2.cu, attention.cu, head.cu).
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "gemm.h"
+
+namespace vipt {
+
+int launch_crop(const uint8_t* const* frames, const int* frame_hw, const double* boxes, double factor, int S,
+                int row_base, int rows_per_seq, void* apatch, int64_t group_stride, double* geom, int* err, int B,
+                cudaStream_t st);
+int launch_patchify(const float* img, int S, int row_base, int rows_per_seq, void* apatch, int64_t group_stride, int B,
+                    cudaStream_t st);
+
+int launch_ln_rows(const float* x_in, int n_in, const int* perm, int perm_stride, float* x_out, void* xn,
+                   const float* gamma, const float* beta, int B, int n_out, int lens_t, cudaStream_t st);
+int launch_prompt_a(const float* xa, int n_cur, const int* slot_of_pos, const float* xd_src, const float* wg_a,
+                    const float* wg_d, const float* sc, float* xd, int B, int lens_t, int lens_full, cudaStream_t st);
+int launch_prompt_b(const float* xd, const float* w1, const float* b1, float smooth, float* P, const float* base,
+                    float* x, int n_cur, const int* slot_of_pos, const float* pos_embed, const float* gamma1,
+                    const float* beta1, void* xn, int B, int lens_t, int lens_full, cudaStream_t st);
+int launch_ce_topk(const float* ce_prob, int n_heads, int n_s, int n_keep, const int* gi_in, int* gi_out, int* perm,
+                   int* removed, int* slot_of_pos, float* score_out, int lens_x, int B, cudaStream_t st);
+int launch_final_norm(const float* x, int n_cur, const int* slot_of_pos, const float* gamma, const float* beta,
+                      void* feat16, float* feat32, int B, int lens_t, int lens_full, cudaStream_t st);
+
+struct AttnOp {
+  CUtensorMap tm;
+  int B, N, nkp;
+};
+int attention_plan(AttnOp* op, const void* qkv, int B, int N);
+int attention_launch(const AttnOp& op, void* out, float* ce_prob, int ce_row, int lens_t, int ce_stride,
+                     cudaStream_t st);
+
+int launch_im2col(const void* in, int c_total, int cin, int cin_stride, void* out, int B, int T, cudaStream_t st);
+int launch_head_final(const void* h4, const float* w5, const float* b5, const float* window, float* score_map,
+                      float* size_map, float* offset_map, float* pred_boxes, double* state, const double* geom,
+                      const int* frame_hw, double* out_boxes, float* out_scores, int B, cudaStream_t st);
+
+}  // namespace vipt

@@ -1,0 +1,287 @@
+// Prompt phase B (Fovea softmax + 8 -> 768 up-projection + residual + next LayerNorm), the
+// candidate-elimination ranking, and the final norm + scatter.  See tokens.cu for the reference sites.
+#include "kernels.h"
+#include "sm100_ptx.cuh"
+
+namespace vipt {
+
+constexpr int D = 768;
+constexpr float kLnEps = 1e-6f;
+constexpr int kTileTok = 16;     // full-grid positions per CTA
+constexpr int kBThreads = 192;   // 4 channels per thread
+
+__device__ __forceinline__ float warp_sum2(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// grid: B * (lens_full / 16).  Tile = 16 consecutive positions of one softmax domain (template
+// positions [0,64) or search positions [64,320): separate Prompt_block calls, vit_ce_prompt.py:212-213).
+//   p          = conv1x1( softmax_pos(x0*smooth) * x0 + x1 )          -> prompt stream P (all positions)
+//   x[row]     = base[row] + p (+ pos_embed at layer 0)               -> kept positions only
+//   xn[row]    = LayerNorm_norm1(x[row]) in fp16                      -> feeds the qkv GEMM
+__global__ void __launch_bounds__(kBThreads)
+prompt_b_kernel(const float* __restrict__ xd, const float* __restrict__ w1, const float* __restrict__ b1, float smooth,
+                float* __restrict__ P, const float* base, float* x, int n_cur,   // base may alias x (in-place)
+                const int* __restrict__ slot_of_pos, const float* __restrict__ pos_embed,
+                const float* __restrict__ gamma1, const float* __restrict__ beta1, op_t* __restrict__ xn, int lens_t,
+                int lens_full) {
+  __shared__ float s_red[8][8];       // per-channel partial max / sum
+  __shared__ float s_max[8], s_inv[8];
+  __shared__ float s_f[kTileTok][8];
+  __shared__ float s_part[kTileTok][6][2];
+  __shared__ int s_row[kTileTok];
+  const int tid = threadIdx.x;
+  const int tiles_per_b = lens_full / kTileTok;
+  const int b = blockIdx.x / tiles_per_b;
+  const int t0 = (blockIdx.x % tiles_per_b) * kTileTok;
+  const int dom0 = t0 < lens_t ? 0 : lens_t;
+  const int domL = t0 < lens_t ? lens_t : lens_full - lens_t;
+  const float* xd_b = xd + (size_t)b * lens_full * 16;
+
+  // ---- Fovea softmax statistics over the domain's positions, per channel (threads 0..63)
+  if (tid < 64) {
+    const int k = tid >> 3, sub = tid & 7;
+    float m = -INFINITY;
+    for (int p = sub; p < domL; p += 8) m = fmaxf(m, xd_b[(dom0 + p) * 16 + k] * smooth);
+    s_red[k][sub] = m;
+  }
+  __syncthreads();
+  if (tid < 8) {
+    float m = s_red[tid][0];
+#pragma unroll
+    for (int i = 1; i < 8; ++i) m = fmaxf(m, s_red[tid][i]);
+    s_max[tid] = m;
+  }
+  __syncthreads();
+  if (tid < 64) {
+    const int k = tid >> 3, sub = tid & 7;
+    const float m = s_max[k];
+    float s = 0.f;
+    for (int p = sub; p < domL; p += 8) s += expf(xd_b[(dom0 + p) * 16 + k] * smooth - m);
+    s_red[k][sub] = s;
+  }
+  __syncthreads();
+  if (tid < 8) {
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s += s_red[tid][i];
+    s_inv[tid] = 1.0f / s;
+  }
+  if (tid >= 64 && tid < 64 + kTileTok) {
+    const int tt = tid - 64, t = t0 + tt;
+    int r = t;
+    if (t >= lens_t && slot_of_pos) {
+      const int s = slot_of_pos[b * (lens_full - lens_t) + (t - lens_t)];
+      r = s < 0 ? -1 : lens_t + s;
+    }
+    s_row[tt] = r;
+  }
+  __syncthreads();
+  if (tid < kTileTok * 8) {
+    const int tt = tid >> 3, k = tid & 7;
+    const float x0 = xd_b[(t0 + tt) * 16 + k], x1 = xd_b[(t0 + tt) * 16 + 8 + k];
+    const float mask = expf(x0 * smooth - s_max[k]) * s_inv[k];
+    s_f[tt][k] = mask * x0 + x1;
+  }
+  __syncthreads();
+
+  // ---- up-projection: this thread owns channels c0..c0+3
+  const int c0 = tid * 4;
+  float w[4][8];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float4 lo = *reinterpret_cast<const float4*>(w1 + (c0 + i) * 8);
+    const float4 hi = *reinterpret_cast<const float4*>(w1 + (c0 + i) * 8 + 4);
+    w[i][0] = lo.x; w[i][1] = lo.y; w[i][2] = lo.z; w[i][3] = lo.w;
+    w[i][4] = hi.x; w[i][5] = hi.y; w[i][6] = hi.z; w[i][7] = hi.w;
+  }
+  const float4 bias = *reinterpret_cast<const float4*>(b1 + c0);
+  float4 xv[kTileTok];
+  const int warp = tid >> 5, lane = tid & 31;
+#pragma unroll
+  for (int tt = 0; tt < kTileTok; ++tt) {
+    float p[4] = {bias.x, bias.y, bias.z, bias.w};
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const float f = s_f[tt][k];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) p[i] += w[i][k] * f;
+    }
+    const int t = t0 + tt;
+    *reinterpret_cast<float4*>(P + ((size_t)b * lens_full + t) * D + c0) = make_float4(p[0], p[1], p[2], p[3]);
+    const int r = s_row[tt];
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (r >= 0) {
+      v = *reinterpret_cast<const float4*>(base + ((size_t)b * n_cur + r) * D + c0);
+      v.x += p[0]; v.y += p[1]; v.z += p[2]; v.w += p[3];
+      if (pos_embed) {
+        const float4 pe = *reinterpret_cast<const float4*>(pos_embed + (size_t)t * D + c0);
+        v.x += pe.x; v.y += pe.y; v.z += pe.z; v.w += pe.w;
+      }
+      *reinterpret_cast<float4*>(x + ((size_t)b * n_cur + r) * D + c0) = v;
+    }
+    xv[tt] = v;
+    const float s = warp_sum2(v.x + v.y + v.z + v.w);
+    if (lane == 0) s_part[tt][warp][0] = s;
+  }
+  __syncthreads();
+  // two-pass variance (mean first), like torch's LayerNorm
+  float mean[kTileTok];
+#pragma unroll
+  for (int tt = 0; tt < kTileTok; ++tt) {
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) s += s_part[tt][i][0];
+    mean[tt] = s * (1.0f / D);
+    const float a = xv[tt].x - mean[tt], bb = xv[tt].y - mean[tt], c = xv[tt].z - mean[tt], d = xv[tt].w - mean[tt];
+    const float q = warp_sum2(a * a + bb * bb + c * c + d * d);
+    if (lane == 0) s_part[tt][warp][1] = q;
+  }
+  __syncthreads();
+  const float4 g = *reinterpret_cast<const float4*>(gamma1 + c0);
+  const float4 be = *reinterpret_cast<const float4*>(beta1 + c0);
+#pragma unroll
+  for (int tt = 0; tt < kTileTok; ++tt) {
+    const int r = s_row[tt];
+    if (r < 0) continue;
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) q += s_part[tt][i][1];
+    const float rstd = rsqrtf(q * (1.0f / D) + kLnEps);
+    uint2 u;
+    u.x = pack_op2((xv[tt].x - mean[tt]) * rstd * g.x + be.x, (xv[tt].y - mean[tt]) * rstd * g.y + be.y);
+    u.y = pack_op2((xv[tt].z - mean[tt]) * rstd * g.z + be.z, (xv[tt].w - mean[tt]) * rstd * g.w + be.w);
+    *reinterpret_cast<uint2*>(xn + ((size_t)b * n_cur + r) * D + c0) = u;
+  }
+}
+
+int launch_prompt_b(const float* xd, const float* w1, const float* b1, float smooth, float* P, const float* base,
+                    float* x, int n_cur, const int* slot_of_pos, const float* pos_embed, const float* gamma1,
+                    const float* beta1, void* xn, int B, int lens_t, int lens_full, cudaStream_t st) {
+  prompt_b_kernel<<<B * (lens_full / kTileTok), kBThreads, 0, st>>>(xd, w1, b1, smooth, P, base, x, n_cur, slot_of_pos,
+                                                                     pos_embed, gamma1, beta1,
+                                                                     reinterpret_cast<op_t*>(xn), lens_t, lens_full);
+  return cudaGetLastError() == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Candidate elimination ranking (attn_blocks.py:37-63).  One CTA per sequence.
+//   score[j] = mean over heads of softmax prob (template token 27 -> search key j)
+//   descending sort (ties: lower slot first), keep the first n_keep.
+// Outputs: perm[r] = old slot of new slot r (r < n_keep); gi_out[r] = original raster position of new
+// slot r; removed[r - n_keep] = raster positions of the dropped tokens in sorted order;
+// slot_of_pos[pos] = new slot or -1.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+ce_topk_kernel(const float* __restrict__ ce_prob, int n_heads, int n_s, int n_keep, const int* __restrict__ gi_in,
+               int* __restrict__ gi_out, int* __restrict__ perm, int* __restrict__ removed,
+               int* __restrict__ slot_of_pos, float* __restrict__ score_out, int lens_x) {
+  __shared__ float s_score[256];
+  const int b = blockIdx.x, j = threadIdx.x;
+  float sc = -INFINITY;
+  if (j < n_s) {
+    float s = 0.f;
+    for (int h = 0; h < n_heads; ++h) s += ce_prob[((size_t)b * n_heads + h) * lens_x + j];
+    sc = s / (float)n_heads;
+    if (score_out) score_out[b * lens_x + j] = sc;
+  }
+  s_score[j] = sc;
+  __syncthreads();
+  if (j >= n_s) return;
+  int rank = 0;
+  for (int i = 0; i < n_s; ++i) {
+    const float o = s_score[i];
+    rank += (o > sc) || (o == sc && i < j);
+  }
+  const int pos = gi_in[b * lens_x + j];
+  if (rank < n_keep) {
+    perm[b * lens_x + rank] = j;
+    gi_out[b * lens_x + rank] = pos;
+    slot_of_pos[b * lens_x + pos] = rank;
+  } else {
+    removed[b * lens_x + (rank - n_keep)] = pos;
+    slot_of_pos[b * lens_x + pos] = -1;
+  }
+}
+
+int launch_ce_topk(const float* ce_prob, int n_heads, int n_s, int n_keep, const int* gi_in, int* gi_out, int* perm,
+                   int* removed, int* slot_of_pos, float* score_out, int lens_x, int B, cudaStream_t st) {
+  if (n_s > 256) return VIPT_ERR_ARG;
+  ce_topk_kernel<<<B, 256, 0, st>>>(ce_prob, n_heads, n_s, n_keep, gi_in, gi_out, perm, removed, slot_of_pos, score_out,
+                                    lens_x);
+  return cudaGetLastError() == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Final norm + recover (vit_ce_prompt.py:318-339): LN of the surviving rows, search rows scattered to
+// raster order, removed positions EXACT zeros.  feat16 (B, 256, 768) feeds the head; feat32
+// (B, 320, 768), optional, is the `backbone_feat` the model API returns.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+final_norm_kernel(const float* __restrict__ x, int n_cur, const int* __restrict__ slot_of_pos,
+                  const float* __restrict__ gamma, const float* __restrict__ beta, op_t* __restrict__ feat16,
+                  float* __restrict__ feat32, int B, int lens_t, int lens_full) {
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (row >= B * lens_full) return;
+  const int b = row / lens_full, t = row % lens_full;
+  int r = t;
+  if (t >= lens_t && slot_of_pos) {
+    const int s = slot_of_pos[b * (lens_full - lens_t) + (t - lens_t)];
+    r = s < 0 ? -1 : lens_t + s;
+  }
+  if (t < lens_t && !feat32) return;
+  float o[6][4];
+  if (r >= 0) {
+    const float* src = x + ((size_t)b * n_cur + r) * D;
+    float4 v[6];
+    float s = 0.f;
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+      v[j] = reinterpret_cast<const float4*>(src)[lane + 32 * j];
+      s += v[j].x + v[j].y + v[j].z + v[j].w;
+    }
+    const float mean = warp_sum2(s) * (1.0f / D);
+    float q = 0.f;
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+      const float a = v[j].x - mean, bb = v[j].y - mean, c = v[j].z - mean, d = v[j].w - mean;
+      q += a * a + bb * bb + c * c + d * d;
+    }
+    const float rstd = rsqrtf(warp_sum2(q) * (1.0f / D) + kLnEps);
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+      const int c = (lane + 32 * j) * 4;
+      const float4 g = *reinterpret_cast<const float4*>(gamma + c);
+      const float4 be = *reinterpret_cast<const float4*>(beta + c);
+      o[j][0] = (v[j].x - mean) * rstd * g.x + be.x; o[j][1] = (v[j].y - mean) * rstd * g.y + be.y;
+      o[j][2] = (v[j].z - mean) * rstd * g.z + be.z; o[j][3] = (v[j].w - mean) * rstd * g.w + be.w;
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 6; ++j) o[j][0] = o[j][1] = o[j][2] = o[j][3] = 0.f;
+  }
+#pragma unroll
+  for (int j = 0; j < 6; ++j) {
+    const int c = (lane + 32 * j) * 4;
+    if (feat32) *reinterpret_cast<float4*>(feat32 + (size_t)row * D + c) = make_float4(o[j][0], o[j][1], o[j][2], o[j][3]);
+    if (t >= lens_t) {
+      uint2 u;
+      u.x = pack_op2(o[j][0], o[j][1]);
+      u.y = pack_op2(o[j][2], o[j][3]);
+      *reinterpret_cast<uint2*>(feat16 + ((size_t)b * (lens_full - lens_t) + (t - lens_t)) * D + c) = u;
+    }
+  }
+}
+
+int launch_final_norm(const float* x, int n_cur, const int* slot_of_pos, const float* gamma, const float* beta,
+                      void* feat16, float* feat32, int B, int lens_t, int lens_full, cudaStream_t st) {
+  const int rows = B * lens_full;
+  final_norm_kernel<<<(rows + 7) / 8, 256, 0, st>>>(x, n_cur, slot_of_pos, gamma, beta, reinterpret_cast<op_t*>(feat16),
+                                                    feat32, B, lens_t, lens_full);
+  return cudaGetLastError() == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
+}
+
+}  // namespace vipt

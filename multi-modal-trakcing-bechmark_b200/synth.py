@@ -36,7 +36,7 @@ def _xavier(g, shape):
     return (torch.rand(shape, generator=g) * 2 - 1) * a
 
 
-def synthetic_state_dict(prompt_type: str = "vipt_deep", seed: int = 0, qkv_std: float = 0.05):
+def synthetic_state_dict(prompt_type: str = "vipt_deep", seed: int = 0, qkv_std: float = 0.02):
     """name -> fp32 tensor, in the reference's state_dict order."""
     assert prompt_type in ("vipt_deep", "vipt_shaw")
     g = torch.Generator().manual_seed(seed)
@@ -97,7 +97,7 @@ def synthetic_state_dict(prompt_type: str = "vipt_deep", seed: int = 0, qkv_std:
         w = _xavier(g, (nout, chans[4], 1, 1))
         b = 0.05 * n(nout)
         if tower == "ctr":
-            w = w * 20.0                                      # score-map contrast
+            w = w * 5.0                                       # score-map contrast without saturating the clamp
         if tower == "size":
             b = torch.full((nout,), math.log(0.25 / 0.75))    # sigmoid -> 0.25: stable box size
         sd[p + "weight"] = w
@@ -160,3 +160,36 @@ def synthetic_sequence(seed: int, n_frames: int, modality: str = "rgbt", box_wh=
         frames[t, :, :, 3:] = np.clip(aux * 255.0, 0, 255).astype(np.uint8)
         boxes[t] = (x0, y0, bw, bh)
     return frames, [float(v) for v in boxes[0]], boxes
+
+
+_KEYS_CACHE = {}
+
+
+def synthetic_state_dict_keys(prompt_type):
+    """Key set of the reference state_dict (used for strict loading)."""
+    if prompt_type not in _KEYS_CACHE:
+        keys = []
+        bb = "backbone."
+        keys += [bb + k for k in ("cls_token", "pos_embed", "pos_embed_z", "pos_embed_x")]
+        for pe in ("patch_embed", "patch_embed_prompt"):
+            keys += [bb + pe + ".proj.weight", bb + pe + ".proj.bias"]
+        n_prompt = DEPTH if prompt_type == "vipt_deep" else 1
+        for i in range(n_prompt):
+            p = bb + "prompt_blocks.%d." % i
+            keys += [p + s for s in ("conv0_0.weight", "conv0_0.bias", "conv0_1.weight", "conv0_1.bias",
+                                     "conv1x1.weight", "conv1x1.bias", "fovea.smooth")]
+        for i in range(n_prompt):
+            keys += [bb + "prompt_norms.%d.weight" % i, bb + "prompt_norms.%d.bias" % i]
+        for i in range(DEPTH):
+            p = bb + "blocks.%d." % i
+            for m in ("norm1", "attn.qkv", "attn.proj", "norm2", "mlp.fc1", "mlp.fc2"):
+                keys += [p + m + ".weight", p + m + ".bias"]
+        keys += [bb + "norm.weight", bb + "norm.bias"]
+        for tower in ("ctr", "offset", "size"):
+            for li in range(1, 5):
+                p = "box_head.conv%d_%s." % (li, tower)
+                keys += [p + s for s in ("0.weight", "0.bias", "1.weight", "1.bias", "1.running_mean",
+                                         "1.running_var", "1.num_batches_tracked")]
+            keys += ["box_head.conv5_%s.weight" % tower, "box_head.conv5_%s.bias" % tower]
+        _KEYS_CACHE[prompt_type] = keys
+    return _KEYS_CACHE[prompt_type]
