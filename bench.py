@@ -1,0 +1,351 @@
+#!/usr/bin/env python
+"""Benchmark of the B200-native ViPT tracking forward (BASELINE.json metric: ViPT-deep frames/s).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--batch B] [--impl reference]
+
+Workload (BASELINE.json configs[1]): ViPT-deep RGBT, LasHeR-shaped 630x480x6 frames, 64 concurrent
+synthetic sequences per B200, template 128 / search 256, fp16 tensor-core operands (fp32 accumulate).
+One "step" = one tracking step of all 64 sequences of a GPU: crop -> backbone -> head -> box update.
+
+  value : frames/s, frames resident in HBM, CUDA-graph replay, no host synchronisation in the loop
+  e2e   : frames/s through the public tracker API with HOST frames: every step copies that step's
+          frames from pinned host memory and reads the boxes back
+  roofline     : tensor-pipe fraction of the tcgen05 GEMM kernel (CUDA events around every launch)
+  cpu_baseline : the oracle port of the reference's CPU path timed on this box's host cores
+
+Multi-GPU (torchrun, one rank per GPU): sequences are sharded rank-wise, weak scaling, no collective
+on the hot path; a final all_gather of the boxes.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+MODALITY = "rgbt"
+PROMPT = "vipt_deep"
+RING = 8                # distinct frame sets cycled through (8 x 116 MB > L2)
+N_DISTINCT = 16         # distinct synthetic sequences; sequence i uses seed i % N_DISTINCT with its own frame phase
+
+# Algorithmic FLOPs per frame: 2*M*N*K at the reference's token counts
+GF_LINEAR = 0.755 + 39.306      # patch embed + qkv/proj/fc1/fc2
+GF_HEAD = 3.313
+GF_ATTN = 2.283
+GF_PROMPT = 0.142
+GF_TOTAL = 45.798
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return d, "measured"
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows = []
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), [c.strip() for c in line.split(",")]))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        rows = [r for ts, r in self.rows if t0 - 0.05 <= ts <= t1 + 0.15 and len(r) >= 7] or \
+               [r for _, r in self.rows if len(r) >= 7]
+        if not rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        sm = sorted(float(r[0]) for r in rows)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(r[3 + i].lower().startswith("active") for r in rows)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(rows[0][1]), "reasons": reasons,
+                "power_w_max": max(float(r[2]) for r in rows), "samples": len(rows)}
+
+
+def make_sequences(batch, rank):
+    """RING host frames + init box for `batch` sequences of this rank (pinned uint8 (RING, H, W, 6))."""
+    from vipt_b200 import synth
+    base = [synth.synthetic_sequence(1000 + s, RING + 1, MODALITY) for s in range(N_DISTINCT)]
+    seqs = []
+    for i in range(batch):
+        frames, box0, _ = base[(i + rank * batch) % N_DISTINCT]
+        seqs.append((frames, box0))
+    return seqs
+
+
+def run_ours(args):
+    import torch.distributed as dist
+    from vipt_b200 import synth
+    from vipt_b200.tracker import BatchedViPTTracker
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    B, K, W = args.batch, args.steps, args.warmup
+    sd = synth.synthetic_state_dict(PROMPT, 0)
+    seqs = make_sequences(B, rank)
+    trk = BatchedViPTTracker(sd, B, PROMPT, use_graph=True)
+    eng = trk.engine
+
+    # ---- host (pinned) and device copies of the frames: ring of RING frame sets, all > L2 together
+    host = [[torch.from_numpy(np.ascontiguousarray(f[t])).pin_memory() for f, _ in seqs] for t in range(RING + 1)]
+    with torch.cuda.stream(eng.stream):
+        devf = [[h.to(dev, non_blocking=True) for h in host[t]] for t in range(RING + 1)]
+        ptrs = [torch.tensor([f.data_ptr() for f in devf[t]], dtype=torch.int64).to(dev) for t in range(RING + 1)]
+    eng.stream.synchronize()
+    boxes0 = [b for _, b in seqs]
+    frame_bytes = sum(int(h.numel()) for h in host[1])
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ================= value: frames resident in HBM, graph replay, no host sync inside the loop
+    trk.initialize(devf[0], boxes0)
+    for k in range(W):
+        eng.track_enqueue(ptrs[1 + k % RING], True)
+    eng.results()
+    barrier()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    time.sleep(0.3)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.time()
+    with torch.cuda.stream(eng.stream):
+        ev0.record()
+        for k in range(K):
+            eng.track_enqueue(ptrs[1 + (W + k) % RING], True)
+        ev1.record()
+    eng.stream.synchronize()
+    barrier()
+    t1 = time.time()
+    clocks = sampler.stop(t0, t1) if sampler else None
+    ms = ev0.elapsed_time(ev1)
+    final_boxes, final_scores = eng.results()
+    launches = eng.info("launches_per_step") * K
+
+    # ================= per-kernel-class device time (CUDA events around every launch, un-graphed)
+    prof = {}
+    nprof = min(K, 4)
+    for k in range(nprof):
+        p = eng.profile_step(ptrs[1 + k % RING])
+        for name, (t, n) in p.items():
+            a = prof.setdefault(name, [0.0, 0])
+            a[0] += t / nprof; a[1] = n
+
+    # ================= e2e: public tracker API, HOST frames, H2D + D2H every step
+    trk.initialize(host[0], boxes0)
+    for k in range(max(3, min(W, 5))):
+        trk.track(host[1 + k % RING])
+    barrier()
+    Ke = K
+    te0 = time.time()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with torch.cuda.stream(eng.stream):
+        e0.record()
+    for k in range(Ke):
+        trk.track(host[1 + k % RING])
+    with torch.cuda.stream(eng.stream):
+        e1.record()
+    eng.stream.synchronize()
+    barrier()
+    e2e_ms = e0.elapsed_time(e1)
+
+    # ================= max over ranks, final gather of the boxes
+    if world > 1:
+        t = torch.tensor([ms, e2e_ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, e2e_ms = t.tolist()
+        gathered = [torch.zeros(B, 4, dtype=torch.float64, device=dev) for _ in range(world)]
+        dist.all_gather(gathered, torch.from_numpy(final_boxes).to(dev))
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    peaks, peak_src = measured_peaks()
+    frames = B * K * world
+    value = frames / (ms * 1e-3)
+    gemm_ms = prof["gemm_linear"][0] + prof["gemm_head"][0]
+    gemm_flops = (GF_LINEAR + GF_HEAD) * 1e9 * B
+    achieved = gemm_flops / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else None
+    peak = float(peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops")))
+    step_ms_prof = sum(v[0] for v in prof.values())
+    out = {
+        "metric": "ViPT-deep tracking frames/sec (crop+backbone+head+box update)", "value": value, "unit": "frames/s",
+        "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f16", "data": "synthetic",
+        "config": {"workload": "ViPT-deep RGBT (LasHeR-shaped 630x480x6), %d concurrent synthetic sequences per B200, "
+                               "template 128 / search 256, CE 0.7 @ layers 3/6/9" % B,
+                   "sequences_per_gpu": B, "frames_per_step": B * world, "prompt_type": PROMPT,
+                   "operands": "fp16 tensor-core operands, fp32 accumulate, fp32 residual stream",
+                   "l2_policy": "inputs larger than L2: ring of %d frame sets = %.0f MB per GPU" % (RING, RING * frame_bytes / 1e6),
+                   "parallelism": "sequence sharding, %d sequences per rank, no hot-path collective" % B,
+                   "weights": "random-init, seeded (synth.synthetic_state_dict)"},
+        "e2e": {"value": B * Ke * world / (e2e_ms * 1e-3), "unit": "frames/s", "h2d_bytes_per_step": frame_bytes + 8 * B,
+                "d2h_bytes_per_step": B * (32 + 4) + 4, "ms_per_step": e2e_ms / Ke},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+                     "frac": (achieved / peak) if achieved else None, "traffic": None,
+                     "kernel": "vipt::gemm_kernel (tcgen05, all linear + head-conv GEMM launches of a step)",
+                     "peak_source": "%s bf16_tflops_sustained (kernel timed inside a long step)" % peak_src,
+                     "algorithmic_gflop_per_frame": GF_LINEAR + GF_HEAD,
+                     "launches_per_step": prof["gemm_linear"][1] + prof["gemm_head"][1],
+                     "avg_launch_ms": gemm_ms / max(1, prof["gemm_linear"][1] + prof["gemm_head"][1]),
+                     "how": "CUDA-event pair around every launch of one un-graphed step (mean of %d steps)" % nprof,
+                     "whole_step_tflops": GF_TOTAL * 1e9 * B / (ms / K * 1e-3) / 1e12,
+                     "whole_step_frac": GF_TOTAL * 1e9 * B / (ms / K * 1e-3) / 1e12 / peak},
+        "kernel_ms_per_step": {k: round(v[0], 4) for k, v in prof.items()},
+        "kernel_share": {k: round(v[0] / step_ms_prof, 4) for k, v in prof.items()},
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        out["cpu_baseline"] = cpu_baseline(sample_frames=args.cpu_frames)
+    print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the oracle port of the reference's own CPU path (the reference is Python and cannot travel
+# to the GPU box; oracle/vipt_oracle.py is pinned against it, tests/golden/).  cv2 does the resize,
+# exactly like the reference's sample_target.
+# ------------------------------------------------------------------------------------------------
+class CpuBatchTracker:
+    """n sequences, each step = crop per sequence -> ONE batched fp32 forward -> per-sequence box update
+    (gives the CPU its best case: the reference itself runs batch 1 per process)."""
+
+    def __init__(self, n):
+        from oracle import vipt_oracle as vo, crop_oracle as co
+        from vipt_b200 import synth
+        self.vo, self.co = vo, co
+        self.sd = {k: v.float() if v.dtype.is_floating_point else v for k, v in synth.synthetic_state_dict(PROMPT, 0).items()}
+        self.seqs = make_sequences(n, 0)
+        self.n = n
+        try:
+            import cv2  # noqa: F401
+            self.use_cv2 = True
+        except Exception:
+            self.use_cv2 = False
+        self.window = vo.hann2d()
+        self.mask = vo.ce_template_mask(n)
+        self.state = [list(b) for _, b in self.seqs]
+        z = [co.preprocess(co.sample_target(f[0], b, 2.0, 128, self.use_cv2)[0]) for f, b in self.seqs]
+        self.z = torch.from_numpy(np.concatenate(z, 0))
+
+    def step(self, k):
+        vo, co = self.vo, self.co
+        t = 1 + k % RING
+        crops, rfs = [], []
+        for i, (f, _) in enumerate(self.seqs):
+            p, rf = co.sample_target(f[t], self.state[i], 4.0, 256, self.use_cv2)
+            crops.append(co.preprocess(p)); rfs.append(rf)
+        x = torch.from_numpy(np.concatenate(crops, 0))
+        with torch.no_grad():
+            out = vo.model_forward(self.sd, self.z, x, self.mask, PROMPT)
+            bbox, best = vo.cal_bbox(self.window * out["score_map"], out["size_map"], out["offset_map"])
+        for i, (f, _) in enumerate(self.seqs):
+            H, W = f.shape[1:3]
+            cx, cy, w, h = (bbox[i] * 256 / rfs[i]).tolist()
+            st = self.state[i]
+            half = 0.5 * 256 / rfs[i]
+            cxr = cx + (st[0] + 0.5 * st[2] - half); cyr = cy + (st[1] + 0.5 * st[3] - half)
+            self.state[i] = vo.clip_box([cxr - 0.5 * w, cyr - 0.5 * h, w, h], H, W, margin=10)
+
+
+def cpu_baseline(sample_frames=64, batch=8):
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    trk = CpuBatchTracker(batch)
+    trk.step(0)                                    # warm-up
+    steps = max(1, sample_frames // batch)
+    t0 = time.time()
+    for k in range(steps):
+        trk.step(1 + k)
+    dt = time.time() - t0
+    return {"value": steps * batch / dt, "unit": "frames/s", "cores": cores, "kind": "port",
+            "sample": "%d frames = %d sequences x %d steps of the same workload, batched fp32 torch-CPU forward "
+                      "(oracle/vipt_oracle.py, cv2 resize), %d threads" % (steps * batch, batch, steps, cores),
+            "seconds": dt}
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the path (oracle port) on the host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    n = args.ref_batch
+    trk = CpuBatchTracker(n)
+    for k in range(args.warmup):
+        trk.step(k)
+    t0 = time.time()
+    for k in range(args.steps):
+        trk.step(args.warmup + k)
+    dt = time.time() - t0
+    value = n * args.steps / dt
+    sample = "each step = %d frames (%d sequences x 1 frame) of the ViPT-deep RGBT workload, fp32, %d host threads" % (n, n, cores)
+    out = {"impl": "reference", "metric": "ViPT-deep tracking frames/sec (crop+backbone+head+box update)",
+           "value": value, "unit": "frames/s", "n_gpus": int(os.environ.get("WORLD_SIZE", "1")), "steps": args.steps,
+           "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+           "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "config": {"workload": "ViPT-deep RGBT (LasHeR-shaped 630x480x6), template 128 / search 256, CE 0.7 @ layers 3/6/9; "
+                                  "bounded sample: " + sample, "prompt_type": PROMPT},
+           "cpu_baseline": {"value": value, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample},
+           "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+           "gpu_launches": 0}
+    print(json.dumps(out))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--batch", type=int, default=64, help="concurrent sequences per GPU")
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--ref-batch", type=int, default=8)
+    ap.add_argument("--cpu-frames", type=int, default=96)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -67,6 +67,11 @@ int vipt_engine_init(void* engine, const void* const* frame_dev_ptrs_host, const
 int vipt_engine_track_enqueue(void* engine, const void* frame_ptrs_dev, int use_graph, void* stream);
 /* copies the latest boxes (B,4) [x,y,w,h] and best scores (B) to host memory and synchronises the stream. */
 int vipt_engine_results(void* engine, double* boxes_host, float* scores_host, void* stream);
+/* one un-graphed step with a CUDA-event pair around every kernel launch; sums (ms) and launch counts per
+ * kernel class: 0 linear GEMMs, 1 head conv GEMMs, 2 attention, 3 prompt blocks, 4 LayerNorm/CE/final,
+ * 5 crop, 6 im2col, 7 head tail.  Used by bench.py for the roofline line. */
+int vipt_engine_profile_step(void* engine, const void* frame_ptrs_dev, float* ms_by_class_host, int* n_by_class_host,
+                             void* stream);
 int64_t vipt_engine_info(void* engine, const char* what);
 int vipt_engine_buffer(void* engine, const char* name, void** dev_ptr, int64_t* bytes);
 

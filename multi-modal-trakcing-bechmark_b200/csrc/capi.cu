@@ -82,6 +82,11 @@ int vipt_engine_track_enqueue(void* e, const void* frame_ptrs_dev, int use_graph
   if (!e || !frame_ptrs_dev) return VIPT_ERR_ARG;
   return ((vipt::Engine*)e)->track_enqueue(frame_ptrs_dev, use_graph != 0, (cudaStream_t)stream);
 }
+int vipt_engine_profile_step(void* e, const void* frame_ptrs_dev, float* ms_by_class_host, int* n_by_class_host,
+                             void* stream) {
+  if (!e || !frame_ptrs_dev || !ms_by_class_host || !n_by_class_host) return VIPT_ERR_ARG;
+  return ((vipt::Engine*)e)->profile_step(frame_ptrs_dev, ms_by_class_host, n_by_class_host, (cudaStream_t)stream);
+}
 int vipt_engine_results(void* ev, double* boxes_host, float* scores_host, void* stream) {
   vipt::Engine* e = (vipt::Engine*)ev;
   if (!e || !boxes_host || !scores_host) return VIPT_ERR_ARG;

@@ -30,6 +30,9 @@ struct PromptW {
   float smooth;
 };
 
+enum KernelClass { K_GEMM = 0, K_GEMM_HEAD, K_ATTN, K_PROMPT, K_NORM, K_CROP, K_IM2COL, K_HEAD_FINAL, K_NUM_CLASSES };
+struct ProfRec { int cls; cudaEvent_t a, b; };
+
 struct Engine {
   int B = 0;               // concurrent sequences (fixed)
   bool deep = true;
@@ -73,6 +76,11 @@ struct Engine {
   // CUDA graph of one tracking step
   cudaGraphExec_t graph_exec = nullptr;
   long launches_per_step = 0;
+
+  std::vector<ProfRec>* prof = nullptr;
+  void prof_begin(int cls, cudaStream_t st);
+  void prof_end(cudaStream_t st);
+  int profile_step(const void* frame_ptrs_dev, float* ms_by_class, int* n_by_class, cudaStream_t st);
 
   ~Engine();
   void* dalloc(size_t bytes);

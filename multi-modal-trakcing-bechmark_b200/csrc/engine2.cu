@@ -20,6 +20,20 @@ namespace vipt {
     if (r_) return r_;  \
   } while (0)
 
+void Engine::prof_begin(int cls, cudaStream_t st) {
+  if (!prof) return;
+  ProfRec r;
+  r.cls = cls;
+  cudaEventCreate(&r.a);
+  cudaEventCreate(&r.b);
+  cudaEventRecord(r.a, st);
+  prof->push_back(r);
+}
+void Engine::prof_end(cudaStream_t st) {
+  if (!prof) return;
+  cudaEventRecord(prof->back().b, st);
+}
+
 int Engine::finalize_buffers() {
   // candidate-elimination schedule: CE_LOC = [3,6,9], keep ratio 0.7 (attn_blocks.py:40)
   int ns = kLensX;
@@ -99,6 +113,14 @@ int Engine::finalize_buffers() {
 int Engine::run_backbone_head(bool tracking, bool want_feat32, int debug_stop, cudaStream_t st) {
   long nl = 0;
   int stage = 0;
+#define LAUNCH(cls, expr)   \
+  do {                      \
+    prof_begin(cls, st);    \
+    int r_ = (expr);        \
+    if (r_) return r_;      \
+    prof_end(st);           \
+    ++nl;                   \
+  } while (0)
 #define STAGE_END()                             \
   do {                                          \
     if (debug_stop > 0 && ++stage == debug_stop) return VIPT_OK; \
@@ -106,13 +128,13 @@ int Engine::run_backbone_head(bool tracking, bool want_feat32, int debug_stop, c
   const size_t RH = (size_t)B * kLensX;
   CK(cudaMemcpyAsync(giA, ident, RH * 4, cudaMemcpyDeviceToDevice, st));
   CK(cudaMemcpyAsync(slot_of_pos, ident, RH * 4, cudaMemcpyDeviceToDevice, st));
-  RET(gemm_launch(g_pe, num_sms, st)); ++nl;
+  LAUNCH(K_GEMM, gemm_launch(g_pe, num_sms, st));
   STAGE_END();   // 1: E
   const float* E0 = E;
   const float* E1 = E + (size_t)B * kLensFull * 768;
-  RET(launch_prompt_a(E0, kLensFull, nullptr, E1, PW[0].wg_a, PW[0].wg_d, PW[0].sc, XD, B, kLensT, kLensFull, st)); ++nl;
-  RET(launch_prompt_b(XD, PW[0].w1, PW[0].b1, PW[0].smooth, P, E0, xA, kLensFull, nullptr, pos_embed, L[0].ln1_g,
-                      L[0].ln1_b, xn, B, kLensT, kLensFull, st)); ++nl;
+  LAUNCH(K_PROMPT, launch_prompt_a(E0, kLensFull, nullptr, E1, PW[0].wg_a, PW[0].wg_d, PW[0].sc, XD, B, kLensT, kLensFull, st));
+  LAUNCH(K_PROMPT, launch_prompt_b(XD, PW[0].w1, PW[0].b1, PW[0].smooth, P, E0, xA, kLensFull, nullptr, pos_embed, L[0].ln1_g,
+                      L[0].ln1_b, xn, B, kLensT, kLensFull, st));
   STAGE_END();   // 2: x, xn, P after the input prompt
   float* x = xA;
   float* x_other = xB;
@@ -123,60 +145,61 @@ int Engine::run_backbone_head(bool tracking, bool want_feat32, int debug_stop, c
     const int n = n_tok[i];
     if (i >= 1) {
       if (deep) {
-        RET(launch_prompt_a(x, n, slot_of_pos, P, PW[i].wg_a, PW[i].wg_d, PW[i].sc, XD, B, kLensT, kLensFull, st)); ++nl;
-        RET(launch_prompt_b(XD, PW[i].w1, PW[i].b1, PW[i].smooth, P, x, x, n, slot_of_pos, nullptr, L[i].ln1_g,
-                            L[i].ln1_b, xn, B, kLensT, kLensFull, st)); ++nl;
+        LAUNCH(K_PROMPT, launch_prompt_a(x, n, slot_of_pos, P, PW[i].wg_a, PW[i].wg_d, PW[i].sc, XD, B, kLensT, kLensFull, st));
+        LAUNCH(K_PROMPT, launch_prompt_b(XD, PW[i].w1, PW[i].b1, PW[i].smooth, P, x, x, n, slot_of_pos, nullptr, L[i].ln1_g,
+                            L[i].ln1_b, xn, B, kLensT, kLensFull, st));
       } else {
-        RET(launch_ln_rows(x, n, nullptr, 0, nullptr, xn, L[i].ln1_g, L[i].ln1_b, B, n, kLensT, st)); ++nl;
+        LAUNCH(K_NORM, launch_ln_rows(x, n, nullptr, 0, nullptr, xn, L[i].ln1_g, L[i].ln1_b, B, n, kLensT, st));
       }
     }
     STAGE_END();   // 3 + 7i: x entering block i, xn = LN1(x)
-    RET(gemm_launch(g_qkv[i], num_sms, st)); ++nl;
+    LAUNCH(K_GEMM, gemm_launch(g_qkv[i], num_sms, st));
     STAGE_END();   // 4 + 7i: qkv
-    RET(attention_launch(a_op[i], att, ce_keep[i] ? ce_prob : nullptr, kCeToken, kLensT, kLensX, st)); ++nl;
+    LAUNCH(K_ATTN, attention_launch(a_op[i], att, ce_keep[i] ? ce_prob : nullptr, kCeToken, kLensT, kLensX, st));
     STAGE_END();   // 5 + 7i: att, ce_prob
     GemmOp gp = g_proj[i];
     gp.p.out = x; gp.p.resid = x;
-    RET(gemm_launch(gp, num_sms, st)); ++nl;
+    LAUNCH(K_GEMM, gemm_launch(gp, num_sms, st));
     STAGE_END();   // 6 + 7i: x after attention residual
     const int nm = n_mlp[i];
     if (ce_keep[i]) {
-      RET(launch_ce_topk(ce_prob, kHeads, n - kLensT, ce_keep[i], gi, gi_other, perm, removed + (size_t)ce_idx * RH,
-                         slot_of_pos, ce_score + (size_t)ce_idx * RH, kLensX, B, st)); ++nl;
-      RET(launch_ln_rows(x, n, perm, kLensX, x_other, xn, L[i].ln2_g, L[i].ln2_b, B, nm, kLensT, st)); ++nl;
+      LAUNCH(K_NORM, launch_ce_topk(ce_prob, kHeads, n - kLensT, ce_keep[i], gi, gi_other, perm, removed + (size_t)ce_idx * RH,
+                         slot_of_pos, ce_score + (size_t)ce_idx * RH, kLensX, B, st));
+      LAUNCH(K_NORM, launch_ln_rows(x, n, perm, kLensX, x_other, xn, L[i].ln2_g, L[i].ln2_b, B, nm, kLensT, st));
       float* t = x; x = x_other; x_other = t;
       int* tg = gi; gi = gi_other; gi_other = tg;
       ++ce_idx;
     } else {
-      RET(launch_ln_rows(x, n, nullptr, 0, nullptr, xn, L[i].ln2_g, L[i].ln2_b, B, nm, kLensT, st)); ++nl;
+      LAUNCH(K_NORM, launch_ln_rows(x, n, nullptr, 0, nullptr, xn, L[i].ln2_g, L[i].ln2_b, B, nm, kLensT, st));
     }
     STAGE_END();   // 7 + 7i: x after CE, xn = LN2(x)
-    RET(gemm_launch(g_fc1[i], num_sms, st)); ++nl;
+    LAUNCH(K_GEMM, gemm_launch(g_fc1[i], num_sms, st));
     STAGE_END();   // 8 + 7i: hbuf
     GemmOp gf = g_fc2[i];
     gf.p.out = x; gf.p.resid = x;
-    RET(gemm_launch(gf, num_sms, st)); ++nl;
+    LAUNCH(K_GEMM, gemm_launch(gf, num_sms, st));
     STAGE_END();   // 9 + 7i: x after the block
   }
   x_final = x;
   gi_final = gi;
-  RET(launch_final_norm(x, n_tok[kDepth], slot_of_pos, norm_g, norm_b, feat16, want_feat32 ? feat32 : nullptr, B, kLensT,
-                        kLensFull, st)); ++nl;
+  LAUNCH(K_NORM, launch_final_norm(x, n_tok[kDepth], slot_of_pos, norm_g, norm_b, feat16, want_feat32 ? feat32 : nullptr, B, kLensT,
+                        kLensFull, st));
   STAGE_END();   // 87: feat16
-  RET(launch_im2col(feat16, 768, 768, 0, a_col, B, 1, st)); ++nl;
-  RET(gemm_launch(g_c1, num_sms, st)); ++nl;
+  LAUNCH(K_IM2COL, launch_im2col(feat16, 768, 768, 0, a_col, B, 1, st));
+  LAUNCH(K_GEMM_HEAD, gemm_launch(g_c1, num_sms, st));
   STAGE_END();   // 88: h1
-  RET(launch_im2col(h1, 768, 256, 256, a_col, B, 3, st)); ++nl;
-  RET(gemm_launch(g_c2, num_sms, st)); ++nl;
-  RET(launch_im2col(h2, 384, 128, 128, a_col, B, 3, st)); ++nl;
-  RET(gemm_launch(g_c3, num_sms, st)); ++nl;
-  RET(launch_im2col(h3, 192, 64, 64, a_col, B, 3, st)); ++nl;
-  RET(gemm_launch(g_c4, num_sms, st)); ++nl;
+  LAUNCH(K_IM2COL, launch_im2col(h1, 768, 256, 256, a_col, B, 3, st));
+  LAUNCH(K_GEMM_HEAD, gemm_launch(g_c2, num_sms, st));
+  LAUNCH(K_IM2COL, launch_im2col(h2, 384, 128, 128, a_col, B, 3, st));
+  LAUNCH(K_GEMM_HEAD, gemm_launch(g_c3, num_sms, st));
+  LAUNCH(K_IM2COL, launch_im2col(h3, 192, 64, 64, a_col, B, 3, st));
+  LAUNCH(K_GEMM_HEAD, gemm_launch(g_c4, num_sms, st));
   STAGE_END();   // 89: h4
-  RET(launch_head_final(h4, w5, b5, window, score_map, size_map, offset_map, pred_boxes, tracking ? state : nullptr,
-                        geom_x, frame_hw, out_boxes, out_scores, B, st)); ++nl;
+  LAUNCH(K_HEAD_FINAL, launch_head_final(h4, w5, b5, window, score_map, size_map, offset_map, pred_boxes, tracking ? state : nullptr,
+                        geom_x, frame_hw, out_boxes, out_scores, B, st));
   launches_per_step = nl;
 #undef STAGE_END
+#undef LAUNCH
   return VIPT_OK;
 }
 
@@ -215,7 +238,9 @@ int Engine::track_enqueue(const void* frame_ptrs_dev, bool use_graph, cudaStream
   const int64_t gs = (int64_t)B * kLensFull * 768;
   auto body = [&](cudaStream_t s) -> int {
     // search: factor 4.0 -> 256 x 256 around the current state (vipt.py:67-69)
+    prof_begin(K_CROP, s);
     RET(launch_crop(frame_ptrs, frame_hw, state, 4.0, 256, kLensT, kLensFull, apatch, gs, geom_x, err, B, s));
+    prof_end(s);
     return run_backbone_head(true, false, 0, s);
   };
   if (!use_graph) {
@@ -235,6 +260,27 @@ int Engine::track_enqueue(const void* frame_ptrs_dev, bool use_graph, cudaStream
   cudaGraphDestroy(graph);
   CK(cudaGraphLaunch(graph_exec, st));
   return VIPT_OK;
+}
+
+// One un-graphed step with a CUDA-event pair around every launch; sums per kernel class.
+int Engine::profile_step(const void* frame_ptrs_dev, float* ms_by_class, int* n_by_class, cudaStream_t st) {
+  std::vector<ProfRec> recs;
+  prof = &recs;
+  int r = track_enqueue(frame_ptrs_dev, false, st);
+  prof = nullptr;
+  cudaError_t e = cudaStreamSynchronize(st);
+  for (int i = 0; i < K_NUM_CLASSES; ++i) { ms_by_class[i] = 0.f; n_by_class[i] = 0; }
+  for (auto& p : recs) {
+    float ms = 0.f;
+    if (e == cudaSuccess && cudaEventElapsedTime(&ms, p.a, p.b) == cudaSuccess) {
+      ms_by_class[p.cls] += ms;
+      n_by_class[p.cls] += 1;
+    }
+    cudaEventDestroy(p.a);
+    cudaEventDestroy(p.b);
+  }
+  if (e != cudaSuccess) return VIPT_ERR_LAUNCH;
+  return r;
 }
 
 }  // namespace vipt

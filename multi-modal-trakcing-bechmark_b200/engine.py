@@ -42,6 +42,8 @@ class NativeEngine:
         self.batch = int(batch)
         self.prompt_type = prompt_type
         h = ctypes.c_void_p()
+        # the engine runs on its own stream: the legacy default stream cannot be graph-captured
+        self.stream = torch.cuda.Stream(device=self.device)
         with torch.cuda.device(self.device):
             _lib.check(self.L.vipt_engine_create(ctypes.byref(h)), "vipt_engine_create")
             self.h = h
@@ -83,8 +85,13 @@ class NativeEngine:
             "engine was built for batch %d" % self.batch
         template = template.to(self.device, torch.float32).contiguous()
         search = search.to(self.device, torch.float32).contiguous()
+        self.stream.wait_stream(torch.cuda.current_stream(self.device))
         _lib.check(self.L.vipt_engine_forward(self.h, _lib.ptr(template), _lib.ptr(search), int(want_feat), int(debug_stop),
-                                              _lib.stream_ptr()), "vipt_engine_forward")
+                                              self._sp()), "vipt_engine_forward")
+        self.stream.synchronize()      # outputs are read by the caller's stream
+
+    def _sp(self):
+        return ctypes.c_void_p(self.stream.cuda_stream)
 
     # ------------------------------------------------------------------ tracking
     def init_sequences(self, frames, boxes):
@@ -95,17 +102,28 @@ class NativeEngine:
         hw = np.ascontiguousarray(np.array([[f.shape[0], f.shape[1]] for f in frames], np.int32))
         bx = np.ascontiguousarray(np.asarray(boxes, np.float64).reshape(self.batch, 4))
         _lib.check(self.L.vipt_engine_init(self.h, ptrs, hw.ctypes.data_as(ctypes.c_void_p),
-                                           bx.ctypes.data_as(ctypes.c_void_p), _lib.stream_ptr()), "vipt_engine_init")
+                                           bx.ctypes.data_as(ctypes.c_void_p), self._sp()), "vipt_engine_init")
 
     def track_enqueue(self, frame_ptrs_dev, use_graph=True):
         """frame_ptrs_dev: int64 CUDA tensor of B frame device pointers.  Asynchronous."""
-        _lib.check(self.L.vipt_engine_track_enqueue(self.h, _lib.ptr(frame_ptrs_dev), int(use_graph), _lib.stream_ptr()),
+        _lib.check(self.L.vipt_engine_track_enqueue(self.h, _lib.ptr(frame_ptrs_dev), int(use_graph), self._sp()),
                    "vipt_engine_track_enqueue")
+
+    KERNEL_CLASSES = ("gemm_linear", "gemm_head", "attention", "prompt", "norm_ce", "crop", "im2col", "head_tail")
+
+    def profile_step(self, frame_ptrs_dev):
+        """{class: (ms, launches)} for one un-graphed step, CUDA events around every launch."""
+        ms = np.zeros(8, np.float32)
+        n = np.zeros(8, np.int32)
+        _lib.check(self.L.vipt_engine_profile_step(self.h, _lib.ptr(frame_ptrs_dev), ms.ctypes.data_as(ctypes.c_void_p),
+                                                   n.ctypes.data_as(ctypes.c_void_p), self._sp()),
+                   "vipt_engine_profile_step")
+        return {k: (float(ms[i]), int(n[i])) for i, k in enumerate(self.KERNEL_CLASSES)}
 
     def results(self):
         boxes = np.empty((self.batch, 4), np.float64)
         scores = np.empty((self.batch,), np.float32)
         _lib.check(self.L.vipt_engine_results(self.h, boxes.ctypes.data_as(ctypes.c_void_p),
-                                              scores.ctypes.data_as(ctypes.c_void_p), _lib.stream_ptr()),
+                                              scores.ctypes.data_as(ctypes.c_void_p), self._sp()),
                    "vipt_engine_results")
         return boxes, scores
