@@ -15,22 +15,36 @@ constexpr int kHd = 64;            // head dim
 constexpr int kQTile = 128;
 constexpr int kMaxKeys = 320;
 constexpr int kAttThreads = 256;
-constexpr int kSQ = 0;                          // 16 KB
-constexpr int kSK = kSQ + kQTile * 128;         // 40 KB
-constexpr int kSV = kSK + kMaxKeys * 128;       // 40 KB
-constexpr int kSP = kSV + kMaxKeys * 128;       // 5 blocks x 16 KB
-constexpr int kSEnd = kSP + (kMaxKeys / 64) * kQTile * 128;
-constexpr int kAttSmem = 1024 + kSEnd + 2 * 2 * kQTile * 4 + 64;
-constexpr uint32_t kTmemO = 384;                // O accumulator columns [384, 448)
+// Shared memory (1024-aligned):  region A | V | softmax scratch | barriers
+//   region A first holds Q (16 KB) and K (64-row boxes), and -- once S = Q K^T has completed -- is
+//   overwritten by P (fp16, 64-key blocks of 128 x 128 B).  V follows.
+// Tensor memory: S occupies columns [0, nkp); O reuses columns [0, 64) after P has been written, so
+// N <= 256 needs 256 columns (two CTAs per SM), N = 320 needs 512.
+constexpr int kSQ = 0;
+constexpr int kSK = kQTile * 128;
+__host__ __device__ constexpr int att_region_a(int nkp) {
+  const int kb = (nkp + 63) / 64;
+  const int qk = kQTile * 128 + kb * 64 * 128;
+  const int p = kb * kQTile * 128;
+  return qk > p ? qk : p;
+}
+__host__ __device__ constexpr int att_scratch_off(int nkp) { return att_region_a(nkp) + ((nkp + 63) / 64) * 64 * 128; }
+__host__ __device__ constexpr int att_smem_bytes(int nkp) {
+  return 1024 + att_scratch_off(nkp) + 2 * 2 * kQTile * 4 + kMaxKeys * 4 + 64;
+}
 
-__global__ void __launch_bounds__(kAttThreads, 1)
+template <uint32_t kTmemCols>
+__global__ void __launch_bounds__(kAttThreads, kTmemCols <= 256 ? 2 : 1)
 attention_kernel(const __grid_constant__ CUtensorMap tm, op_t* __restrict__ out, float* __restrict__ ce_prob,
                  int N, int nkp, int ce_row, int lens_t, int ce_stride, float scale_log2) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  float* s_max = reinterpret_cast<float*>(smem + kSEnd);      // [2][128]
+  const int kSP = 0;                                          // P overwrites Q/K
+  const int kSV = att_region_a(nkp);
+  float* s_max = reinterpret_cast<float*>(smem + att_scratch_off(nkp));   // [2][128]
   float* s_sum = s_max + 2 * kQTile;                          // [2][128]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(s_sum + 2 * kQTile);   // qk, v, s, o
+  float* s_ce = s_sum + 2 * kQTile;                           // [320] un-normalised CE row
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_ce + kMaxKeys);      // qk, v, s, o
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4);
 
   const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
@@ -43,7 +57,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tm, op_t* __restrict__ out,
     for (int i = 0; i < 4; ++i) mbar_init(&bars[i], 1);
     fence_mbar_init();
   }
-  if (warp == 1) tmem_alloc<512>(tmem_slot);
+  if (warp == 1) tmem_alloc<kTmemCols>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -92,8 +106,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tm, op_t* __restrict__ out,
   s_max[hf * kQTile + row] = m;
   __syncthreads();
   m = fmaxf(s_max[row], s_max[kQTile + row]);
-  const bool ce_thread = (ce_prob != nullptr) && (qt == 0) && (row == ce_row);
-  float* ce_dst = ce_prob ? ce_prob + ((size_t)b * gridDim.y + h) * ce_stride : nullptr;
+  const bool ce_cta = (ce_prob != nullptr) && (qt == 0);
+  const bool ce_thread = ce_cta && (row == ce_row);
   float sum = 0.f;
   for (int c = c_begin; c < c_end; ++c) {
     uint32_t v[32];
@@ -106,10 +120,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tm, op_t* __restrict__ out,
       sum += p[j];
     }
     if (ce_thread) {
-      for (int j = 0; j < 32; ++j) {
-        const int col = c * 32 + j;
-        if (col >= lens_t && col < N) ce_dst[col - lens_t] = p[j];
-      }
+#pragma unroll
+      for (int j = 0; j < 32; ++j) s_ce[c * 32 + j] = p[j];
     }
     // P[row][c*32 .. +32) -> swizzled K-major tile: block (c/2), 16-byte chunks (c%2)*4 .. +4
     uint8_t* prow = smem + kSP + (c >> 1) * (kQTile * 128) + row * 128;
@@ -129,12 +141,10 @@ attention_kernel(const __grid_constant__ CUtensorMap tm, op_t* __restrict__ out,
   tc_fence_before();
   __syncthreads();
   const float inv = 1.0f / (s_sum[row] + s_sum[kQTile + row]);
-  if (ce_thread) {
-    for (int c = c_begin; c < c_end; ++c)
-      for (int j = 0; j < 32; ++j) {
-        const int col = c * 32 + j;
-        if (col >= lens_t && col < N) ce_dst[col - lens_t] *= inv;
-      }
+  if (ce_cta) {        // normalised CE row, written cooperatively (coalesced)
+    const float ce_inv = 1.0f / (s_sum[ce_row] + s_sum[kQTile + ce_row]);
+    float* ce_dst = ce_prob + ((size_t)b * gridDim.y + h) * ce_stride;
+    for (int col = lens_t + (int)threadIdx.x; col < N; col += kAttThreads) ce_dst[col - lens_t] = s_ce[col] * ce_inv;
   }
 
   // ---- O = P V
@@ -145,7 +155,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tm, op_t* __restrict__ out,
     for (int j = 0; j < nkp / 16; ++j) {
       const uint64_t pd = make_sdesc_sw128(smem_u32(smem + kSP + (j >> 2) * (kQTile * 128) + (j & 3) * 32));
       const uint64_t vd = make_sdesc_sw128(smem_u32(smem + kSV + j * 16 * 128));
-      umma_f16(tmem + kTmemO, pd, vd, idesc, j != 0);
+      umma_f16(tmem, pd, vd, idesc, j != 0);      // O reuses S columns [0,64)
     }
     umma_commit(&bars[3]);
   }
@@ -154,7 +164,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tm, op_t* __restrict__ out,
   tc_fence_after();
   {
     uint32_t v[32];
-    tmem_ld32(t_row + kTmemO + hf * 32, v);
+    tmem_ld32(t_row + hf * 32, v);
     tmem_ld_wait();
     if (q0 + row < N) {
       op_t* o = out + ((size_t)b * N + q0 + row) * 768 + h * kHd + hf * 32;
@@ -173,7 +183,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tm, op_t* __restrict__ out,
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc<512>(tmem);
+    tmem_dealloc<kTmemCols>(tmem);
   }
 }
 
@@ -192,14 +202,22 @@ int attention_launch(const AttnOp& op, void* out, float* ce_prob, int ce_row, in
                      cudaStream_t st) {
   static bool attr = false;
   if (!attr) {
-    if (cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttSmem) != cudaSuccess)
+    if (cudaFuncSetAttribute(attention_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, att_smem_bytes(256)) !=
+            cudaSuccess ||
+        cudaFuncSetAttribute(attention_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             att_smem_bytes(kMaxKeys)) != cudaSuccess)
       return VIPT_ERR_LAUNCH;
     attr = true;
   }
   dim3 grid((op.N + kQTile - 1) / kQTile, 12, op.B);
   const float scale_log2 = 0.125f * 1.4426950408889634f;
-  attention_kernel<<<grid, kAttThreads, kAttSmem, st>>>(op.tm, reinterpret_cast<op_t*>(out), ce_prob, op.N, op.nkp,
-                                                        ce_row, lens_t, ce_stride, scale_log2);
+  const int smem = att_smem_bytes(op.nkp);
+  if (op.nkp <= 256)
+    attention_kernel<256><<<grid, kAttThreads, smem, st>>>(op.tm, reinterpret_cast<op_t*>(out), ce_prob, op.N, op.nkp,
+                                                           ce_row, lens_t, ce_stride, scale_log2);
+  else
+    attention_kernel<512><<<grid, kAttThreads, smem, st>>>(op.tm, reinterpret_cast<op_t*>(out), ce_prob, op.N, op.nkp,
+                                                           ce_row, lens_t, ce_stride, scale_log2);
   return cudaGetLastError() == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
 }
 

@@ -55,8 +55,8 @@ struct Engine {
   int ce_keep[kDepth];       // 0 if not a CE layer, else number of kept search tokens
 
   // activations
-  __half *apatch, *xn, *qkv, *att, *hbuf, *feat16, *a_col, *h1, *h2, *h3, *h4;
-  float *E, *xA, *xB, *P, *XD, *ce_prob, *ce_score, *feat32;
+  __half *apatch, *xn, *dbuf, *qkv, *att, *hbuf, *feat16, *a_col, *h1, *h2, *h3, *h4;
+  float *E, *xA, *xB, *P, *XD, *FV, *ce_prob, *ce_score, *feat32;
   int *giA, *giB, *perm, *removed, *slot_of_pos, *ident, *err;
   // outputs / state
   float *score_map, *size_map, *offset_map, *pred_boxes, *out_scores;

@@ -57,8 +57,8 @@ int Engine::finalize_buffers() {
   AL(apatch, __half, 2 * R * 768);
   AL(E, float, 2 * R * 768);
   AL(xA, float, R * 768); AL(xB, float, R * 768); AL(P, float, R * 768);
-  AL(XD, float, R * 16);
-  AL(xn, __half, R * 768); AL(qkv, __half, R * 2304); AL(att, __half, R * 768); AL(hbuf, __half, R * 3072);
+  AL(XD, float, R * 16); AL(FV, float, R * 8);
+  AL(xn, __half, R * 768); AL(dbuf, __half, R * 768); AL(qkv, __half, R * 2304); AL(att, __half, R * 768); AL(hbuf, __half, R * 3072);
   AL(ce_prob, float, (size_t)B * kHeads * kLensX); AL(ce_score, float, 3 * RH);
   AL(feat16, __half, RH * 768); AL(feat32, float, R * 768);
   AL(a_col, __half, RH * 6912);        // largest im2col: conv1 (also holds 3 x RH x 2304 etc.)
@@ -88,12 +88,13 @@ int Engine::finalize_buffers() {
     RET(gemm_plan(&g_qkv[i], xn, 768, 0, L[i].w_qkv, 768, 0, 1, Ma, 2304, 768, 256, EPI_BIAS_F16, qkv, 2304, 0, 0,
                   L[i].b_qkv, nullptr));
     RET(attention_plan(&a_op[i], qkv, B, n_tok[i]));
-    // proj / fc2 write the residual stream in place; which of xA/xB is current is patched at run time
-    RET(gemm_plan(&g_proj[i], att, 768, 0, L[i].w_proj, 768, 0, 1, Ma, 768, 768, 256, EPI_RESID_F32, nullptr, 768, 0, 0,
+    // proj / fc2 write their branch output as fp16 (dbuf); the residual add is fused into the next
+    // LayerNorm / prompt kernel, where it is coalesced
+    RET(gemm_plan(&g_proj[i], att, 768, 0, L[i].w_proj, 768, 0, 1, Ma, 768, 768, 256, EPI_BIAS_F16, dbuf, 768, 0, 0,
                   L[i].b_proj, nullptr));
     RET(gemm_plan(&g_fc1[i], xn, 768, 0, L[i].w_fc1, 768, 0, 1, Mm, 3072, 768, 256, EPI_GELU_F16, hbuf, 3072, 0, 0,
                   L[i].b_fc1, nullptr));
-    RET(gemm_plan(&g_fc2[i], hbuf, 3072, 0, L[i].w_fc2, 3072, 0, 1, Mm, 768, 3072, 256, EPI_RESID_F32, nullptr, 768, 0,
+    RET(gemm_plan(&g_fc2[i], hbuf, 3072, 0, L[i].w_fc2, 3072, 0, 1, Mm, 768, 3072, 256, EPI_BIAS_F16, dbuf, 768, 0,
                   0, L[i].b_fc2, nullptr));
   }
   const int MH = B * kLensX;
@@ -132,8 +133,9 @@ int Engine::run_backbone_head(bool tracking, bool want_feat32, int debug_stop, c
   STAGE_END();   // 1: E
   const float* E0 = E;
   const float* E1 = E + (size_t)B * kLensFull * 768;
-  LAUNCH(K_PROMPT, launch_prompt_a(E0, kLensFull, nullptr, E1, PW[0].wg_a, PW[0].wg_d, PW[0].sc, XD, B, kLensT, kLensFull, st));
-  LAUNCH(K_PROMPT, launch_prompt_b(XD, PW[0].w1, PW[0].b1, PW[0].smooth, P, E0, xA, kLensFull, nullptr, pos_embed, L[0].ln1_g,
+  LAUNCH(K_PROMPT, launch_prompt_a(E0, nullptr, kLensFull, nullptr, E1, PW[0].wg_a, PW[0].wg_d, PW[0].sc, XD, B, kLensT, kLensFull, st));
+  LAUNCH(K_PROMPT, launch_fovea(XD, PW[0].smooth, FV, B, kLensT, kLensFull, st));
+  LAUNCH(K_PROMPT, launch_prompt_b(FV, PW[0].w1, PW[0].b1, P, E0, nullptr, xA, kLensFull, nullptr, pos_embed, L[0].ln1_g,
                       L[0].ln1_b, xn, B, kLensT, kLensFull, st));
   STAGE_END();   // 2: x, xn, P after the input prompt
   float* x = xA;
@@ -145,11 +147,12 @@ int Engine::run_backbone_head(bool tracking, bool want_feat32, int debug_stop, c
     const int n = n_tok[i];
     if (i >= 1) {
       if (deep) {
-        LAUNCH(K_PROMPT, launch_prompt_a(x, n, slot_of_pos, P, PW[i].wg_a, PW[i].wg_d, PW[i].sc, XD, B, kLensT, kLensFull, st));
-        LAUNCH(K_PROMPT, launch_prompt_b(XD, PW[i].w1, PW[i].b1, PW[i].smooth, P, x, x, n, slot_of_pos, nullptr, L[i].ln1_g,
+        LAUNCH(K_PROMPT, launch_prompt_a(x, dbuf, n, slot_of_pos, P, PW[i].wg_a, PW[i].wg_d, PW[i].sc, XD, B, kLensT, kLensFull, st));
+        LAUNCH(K_PROMPT, launch_fovea(XD, PW[i].smooth, FV, B, kLensT, kLensFull, st));
+        LAUNCH(K_PROMPT, launch_prompt_b(FV, PW[i].w1, PW[i].b1, P, x, dbuf, x, n, slot_of_pos, nullptr, L[i].ln1_g,
                             L[i].ln1_b, xn, B, kLensT, kLensFull, st));
       } else {
-        LAUNCH(K_NORM, launch_ln_rows(x, n, nullptr, 0, nullptr, xn, L[i].ln1_g, L[i].ln1_b, B, n, kLensT, st));
+        LAUNCH(K_NORM, launch_ln_rows(x, n, dbuf, nullptr, 0, x, xn, L[i].ln1_g, L[i].ln1_b, B, n, kLensT, st));
       }
     }
     STAGE_END();   // 3 + 7i: x entering block i, xn = LN1(x)
@@ -157,32 +160,28 @@ int Engine::run_backbone_head(bool tracking, bool want_feat32, int debug_stop, c
     STAGE_END();   // 4 + 7i: qkv
     LAUNCH(K_ATTN, attention_launch(a_op[i], att, ce_keep[i] ? ce_prob : nullptr, kCeToken, kLensT, kLensX, st));
     STAGE_END();   // 5 + 7i: att, ce_prob
-    GemmOp gp = g_proj[i];
-    gp.p.out = x; gp.p.resid = x;
-    LAUNCH(K_GEMM, gemm_launch(gp, num_sms, st));
-    STAGE_END();   // 6 + 7i: x after attention residual
+    LAUNCH(K_GEMM, gemm_launch(g_proj[i], num_sms, st));
+    STAGE_END();   // 6 + 7i: dbuf = attention branch output
     const int nm = n_mlp[i];
     if (ce_keep[i]) {
       LAUNCH(K_NORM, launch_ce_topk(ce_prob, kHeads, n - kLensT, ce_keep[i], gi, gi_other, perm, removed + (size_t)ce_idx * RH,
                          slot_of_pos, ce_score + (size_t)ce_idx * RH, kLensX, B, st));
-      LAUNCH(K_NORM, launch_ln_rows(x, n, perm, kLensX, x_other, xn, L[i].ln2_g, L[i].ln2_b, B, nm, kLensT, st));
+      LAUNCH(K_NORM, launch_ln_rows(x, n, dbuf, perm, kLensX, x_other, xn, L[i].ln2_g, L[i].ln2_b, B, nm, kLensT, st));
       float* t = x; x = x_other; x_other = t;
       int* tg = gi; gi = gi_other; gi_other = tg;
       ++ce_idx;
     } else {
-      LAUNCH(K_NORM, launch_ln_rows(x, n, nullptr, 0, nullptr, xn, L[i].ln2_g, L[i].ln2_b, B, nm, kLensT, st));
+      LAUNCH(K_NORM, launch_ln_rows(x, n, dbuf, nullptr, 0, x, xn, L[i].ln2_g, L[i].ln2_b, B, nm, kLensT, st));
     }
     STAGE_END();   // 7 + 7i: x after CE, xn = LN2(x)
     LAUNCH(K_GEMM, gemm_launch(g_fc1[i], num_sms, st));
     STAGE_END();   // 8 + 7i: hbuf
-    GemmOp gf = g_fc2[i];
-    gf.p.out = x; gf.p.resid = x;
-    LAUNCH(K_GEMM, gemm_launch(gf, num_sms, st));
-    STAGE_END();   // 9 + 7i: x after the block
+    LAUNCH(K_GEMM, gemm_launch(g_fc2[i], num_sms, st));
+    STAGE_END();   // 9 + 7i: dbuf = MLP branch output
   }
   x_final = x;
   gi_final = gi;
-  LAUNCH(K_NORM, launch_final_norm(x, n_tok[kDepth], slot_of_pos, norm_g, norm_b, feat16, want_feat32 ? feat32 : nullptr, B, kLensT,
+  LAUNCH(K_NORM, launch_final_norm(x, dbuf, n_tok[kDepth], slot_of_pos, norm_g, norm_b, feat16, want_feat32 ? feat32 : nullptr, B, kLensT,
                         kLensFull, st));
   STAGE_END();   // 87: feat16
   LAUNCH(K_IM2COL, launch_im2col(feat16, 768, 768, 0, a_col, B, 1, st));

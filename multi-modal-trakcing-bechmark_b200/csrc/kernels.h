@@ -14,16 +14,17 @@ int launch_crop(const uint8_t* const* frames, const int* frame_hw, const double*
 int launch_patchify(const float* img, int S, int row_base, int rows_per_seq, void* apatch, int64_t group_stride, int B,
                     cudaStream_t st);
 
-int launch_ln_rows(const float* x_in, int n_in, const int* perm, int perm_stride, float* x_out, void* xn,
+int launch_ln_rows(const float* x_in, int n_in, const void* delta, const int* perm, int perm_stride, float* x_out, void* xn,
                    const float* gamma, const float* beta, int B, int n_out, int lens_t, cudaStream_t st);
-int launch_prompt_a(const float* xa, int n_cur, const int* slot_of_pos, const float* xd_src, const float* wg_a,
+int launch_prompt_a(const float* xa, const void* delta, int n_cur, const int* slot_of_pos, const float* xd_src, const float* wg_a,
                     const float* wg_d, const float* sc, float* xd, int B, int lens_t, int lens_full, cudaStream_t st);
-int launch_prompt_b(const float* xd, const float* w1, const float* b1, float smooth, float* P, const float* base,
+int launch_fovea(const float* xd, float smooth, float* F, int B, int lens_t, int lens_full, cudaStream_t st);
+int launch_prompt_b(const float* F, const float* w1, const float* b1, float* P, const float* base, const void* delta,
                     float* x, int n_cur, const int* slot_of_pos, const float* pos_embed, const float* gamma1,
                     const float* beta1, void* xn, int B, int lens_t, int lens_full, cudaStream_t st);
 int launch_ce_topk(const float* ce_prob, int n_heads, int n_s, int n_keep, const int* gi_in, int* gi_out, int* perm,
                    int* removed, int* slot_of_pos, float* score_out, int lens_x, int B, cudaStream_t st);
-int launch_final_norm(const float* x, int n_cur, const int* slot_of_pos, const float* gamma, const float* beta,
+int launch_final_norm(const float* x, const void* delta, int n_cur, const int* slot_of_pos, const float* gamma, const float* beta,
                       void* feat16, float* feat32, int B, int lens_t, int lens_full, cudaStream_t st);
 
 struct AttnOp {

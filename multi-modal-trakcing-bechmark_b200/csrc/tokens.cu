@@ -26,6 +26,20 @@ __device__ __forceinline__ void load_row(const float* row, int lane, float4 (&v)
 #pragma unroll
   for (int j = 0; j < 6; ++j) v[j] = reinterpret_cast<const float4*>(row)[lane + 32 * j];
 }
+// fp16 branch output (attn.proj / mlp.fc2 GEMM result) of the same row: 4 halves per chunk
+__device__ __forceinline__ float4 ld_delta4(const op_t* row, int chunk) {
+  const uint2 u = reinterpret_cast<const uint2*>(row)[chunk];
+  const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&u.x));
+  const float2 b = __half22float2(*reinterpret_cast<const __half2*>(&u.y));
+  return make_float4(a.x, a.y, b.x, b.y);
+}
+__device__ __forceinline__ void add_delta_row(const op_t* drow, int lane, float4 (&v)[6]) {
+#pragma unroll
+  for (int j = 0; j < 6; ++j) {
+    const float4 d = ld_delta4(drow, lane + 32 * j);
+    v[j].x += d.x; v[j].y += d.y; v[j].z += d.z; v[j].w += d.w;
+  }
+}
 
 __device__ __forceinline__ void row_stats(const float4 (&v)[6], float& mean, float& rstd) {
   float s = 0.f;
@@ -56,12 +70,15 @@ __device__ __forceinline__ void store_ln_f16(op_t* out, int lane, const float4 (
 }
 
 // ------------------------------------------------------------------------------------------------
-// LayerNorm rows -> fp16, optionally gathering search rows through `perm` (candidate elimination:
-// new slot r takes old slot perm[b][r]) and copying the gathered fp32 row to x_out.
+// Residual add + LayerNorm:  x_out[row] = x_in[src] + delta[src];  xn[row] = LN(x_out[row]) in fp16.
+// `delta` is the fp16 output of the preceding attn.proj / mlp.fc2 GEMM (the residual add of
+// attn_blocks.py:95,103 happens here, coalesced, instead of in the GEMM epilogue).  `perm` gathers the
+// search rows (candidate elimination: new slot r takes old slot perm[b][r]).  x_out may alias x_in
+// when perm is null.
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-ln_rows_kernel(const float* __restrict__ x_in, int n_in, const int* __restrict__ perm, int perm_stride,
-               float* __restrict__ x_out, op_t* __restrict__ xn, const float* __restrict__ gamma,
+ln_rows_kernel(const float* x_in, int n_in, const op_t* __restrict__ delta, const int* __restrict__ perm, int perm_stride,
+               float* x_out, op_t* __restrict__ xn, const float* __restrict__ gamma,
                const float* __restrict__ beta, int B, int n_out, int lens_t) {
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
@@ -71,6 +88,7 @@ ln_rows_kernel(const float* __restrict__ x_in, int n_in, const int* __restrict__
   if (perm && r >= lens_t) src = lens_t + perm[b * perm_stride + (r - lens_t)];
   float4 v[6];
   load_row(x_in + ((size_t)b * n_in + src) * D, lane, v);
+  if (delta) add_delta_row(delta + ((size_t)b * n_in + src) * D, lane, v);
   if (x_out) {
 #pragma unroll
     for (int j = 0; j < 6; ++j) reinterpret_cast<float4*>(x_out + (size_t)row * D)[lane + 32 * j] = v[j];
@@ -80,10 +98,11 @@ ln_rows_kernel(const float* __restrict__ x_in, int n_in, const int* __restrict__
   store_ln_f16(xn + (size_t)row * D, lane, v, mean, rstd, gamma, beta);
 }
 
-int launch_ln_rows(const float* x_in, int n_in, const int* perm, int perm_stride, float* x_out, void* xn,
+int launch_ln_rows(const float* x_in, int n_in, const void* delta, const int* perm, int perm_stride, float* x_out, void* xn,
                    const float* gamma, const float* beta, int B, int n_out, int lens_t, cudaStream_t st) {
   const int rows = B * n_out;
-  ln_rows_kernel<<<(rows + 7) / 8, 256, 0, st>>>(x_in, n_in, perm, perm_stride, x_out, reinterpret_cast<op_t*>(xn),
+  ln_rows_kernel<<<(rows + 7) / 8, 256, 0, st>>>(x_in, n_in, reinterpret_cast<const op_t*>(delta), perm, perm_stride, x_out,
+                                                 reinterpret_cast<op_t*>(xn),
                                                  gamma, beta, B, n_out, lens_t);
   return cudaGetLastError() == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
 }
@@ -107,9 +126,9 @@ struct PromptAFold {            // device pointers, per layer
   const float* sc;              // [32]: s_a[8], c_a[8], s_d[8], c_d[8]
 };
 
-__global__ void __launch_bounds__(256)
-prompt_a_kernel(const float* __restrict__ xa, int n_cur, const int* __restrict__ slot_of_pos,
-                const float* __restrict__ xd_src, PromptAFold w, float* __restrict__ xd, int B, int lens_t,
+__global__ void __launch_bounds__(256, 2)
+prompt_a_kernel(const float* __restrict__ xa, const op_t* __restrict__ delta, int n_cur,
+                const int* __restrict__ slot_of_pos, const float* __restrict__ xd_src, PromptAFold w, float* __restrict__ xd, int B, int lens_t,
                 int lens_full) {
   extern __shared__ float4 ws4[];    // [2][8][192] float4
   for (int i = threadIdx.x; i < 2 * 8 * 192; i += 256)
@@ -118,14 +137,18 @@ prompt_a_kernel(const float* __restrict__ xa, int n_cur, const int* __restrict__
   __syncthreads();
   const int lane = threadIdx.x & 31;
   const int groups_per_b = lens_full / kTok;
-  for (int wid = blockIdx.x * 8 + (threadIdx.x >> 5); wid < B * groups_per_b; wid += gridDim.x * 8) {
-  const int b = wid / groups_per_b;
-  const int t0 = (wid % groups_per_b) * kTok;
-  for (int stream = 0; stream < 2; ++stream) {
+  const int n_tasks = B * groups_per_b * 2;          // task = (4 consecutive positions, stream)
+  for (int task = blockIdx.x * 8 + (threadIdx.x >> 5); task < n_tasks; task += gridDim.x * 8) {
+    const int stream = task & 1;
+    const int wid = task >> 1;
+    const int b = wid / groups_per_b;
+    const int t0 = (wid % groups_per_b) * kTok;
     const float* rows[kTok];
+    const op_t* drows[kTok];
 #pragma unroll
     for (int tt = 0; tt < kTok; ++tt) {
       const int t = t0 + tt;
+      drows[tt] = nullptr;
       if (stream == 0) {
         int r = t;
         if (t >= lens_t && slot_of_pos) {
@@ -133,6 +156,7 @@ prompt_a_kernel(const float* __restrict__ xa, int n_cur, const int* __restrict__
           r = s < 0 ? -1 : lens_t + s;
         }
         rows[tt] = r < 0 ? nullptr : xa + ((size_t)b * n_cur + r) * D;
+        if (delta && r >= 0) drows[tt] = delta + ((size_t)b * n_cur + r) * D;
       } else {
         rows[tt] = xd_src + ((size_t)b * lens_full + t) * D;
       }
@@ -146,20 +170,35 @@ prompt_a_kernel(const float* __restrict__ xa, int n_cur, const int* __restrict__
     }
     const float4* wbase = ws4 + stream * 8 * 192;
 #pragma unroll
-    for (int j = 0; j < 6; ++j) {
-      float4 v[kTok];
+    for (int half = 0; half < 2; ++half) {
+      float4 v[3][kTok];                       // 12 independent 512-byte row segments in flight per warp
 #pragma unroll
-      for (int tt = 0; tt < kTok; ++tt) {
-        v[tt] = rows[tt] ? reinterpret_cast<const float4*>(rows[tt])[lane + 32 * j] : make_float4(0.f, 0.f, 0.f, 0.f);
-        s1[tt] += v[tt].x + v[tt].y + v[tt].z + v[tt].w;
-        s2[tt] += v[tt].x * v[tt].x + v[tt].y * v[tt].y + v[tt].z * v[tt].z + v[tt].w * v[tt].w;
-      }
-#pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        const float4 wv = wbase[k * 192 + lane + 32 * j];
+      for (int jj = 0; jj < 3; ++jj)
 #pragma unroll
         for (int tt = 0; tt < kTok; ++tt)
-          acc[tt][k] += wv.x * v[tt].x + wv.y * v[tt].y + wv.z * v[tt].z + wv.w * v[tt].w;
+        {
+          v[jj][tt] = rows[tt] ? __ldg(reinterpret_cast<const float4*>(rows[tt]) + lane + 32 * (half * 3 + jj))
+                               : make_float4(0.f, 0.f, 0.f, 0.f);
+          if (drows[tt]) {
+            const float4 d = ld_delta4(drows[tt], lane + 32 * (half * 3 + jj));
+            v[jj][tt].x += d.x; v[jj][tt].y += d.y; v[jj][tt].z += d.z; v[jj][tt].w += d.w;
+          }
+        }
+#pragma unroll
+      for (int jj = 0; jj < 3; ++jj) {
+#pragma unroll
+        for (int tt = 0; tt < kTok; ++tt) {
+          const float4 a = v[jj][tt];
+          s1[tt] += a.x + a.y + a.z + a.w;
+          s2[tt] += a.x * a.x + a.y * a.y + a.z * a.z + a.w * a.w;
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const float4 wv = wbase[k * 192 + lane + 32 * (half * 3 + jj)];
+#pragma unroll
+          for (int tt = 0; tt < kTok; ++tt)
+            acc[tt][k] += wv.x * v[jj][tt].x + wv.y * v[jj][tt].y + wv.z * v[jj][tt].z + wv.w * v[jj][tt].w;
+        }
       }
     }
 #pragma unroll
@@ -177,10 +216,9 @@ prompt_a_kernel(const float* __restrict__ xa, int n_cur, const int* __restrict__
       if (lane < 8) xd[((size_t)b * lens_full + t0 + tt) * 16 + stream * 8 + lane] = mine;
     }
   }
-  }
 }
 
-int launch_prompt_a(const float* xa, int n_cur, const int* slot_of_pos, const float* xd_src, const float* wg_a,
+int launch_prompt_a(const float* xa, const void* delta, int n_cur, const int* slot_of_pos, const float* xd_src, const float* wg_a,
                     const float* wg_d, const float* sc, float* xd, int B, int lens_t, int lens_full, cudaStream_t st) {
   static bool attr = false;
   const int smem = 2 * 8 * 192 * 16;
@@ -190,10 +228,11 @@ int launch_prompt_a(const float* xa, int n_cur, const int* slot_of_pos, const fl
     attr = true;
   }
   PromptAFold w{wg_a, wg_d, sc};
-  const int warps = B * (lens_full / kTok);
-  int grid = (warps + 7) / 8;
-  if (grid > 148 * 3) grid = 148 * 3;      // persistent: the 48 KB weight tile is staged once per CTA
-  prompt_a_kernel<<<grid, 256, smem, st>>>(xa, n_cur, slot_of_pos, xd_src, w, xd, B, lens_t, lens_full);
+  const int tasks = B * (lens_full / kTok) * 2;
+  int grid = (tasks + 7) / 8;
+  if (grid > 148 * 2) grid = 148 * 2;      // persistent: the 48 KB weight tile is staged once per CTA
+  prompt_a_kernel<<<grid, 256, smem, st>>>(xa, reinterpret_cast<const op_t*>(delta), n_cur, slot_of_pos, xd_src, w, xd, B, lens_t,
+                                           lens_full);
   return cudaGetLastError() == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
 }
 

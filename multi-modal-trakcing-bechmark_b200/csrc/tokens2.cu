@@ -7,7 +7,7 @@ namespace vipt {
 
 constexpr int D = 768;
 constexpr float kLnEps = 1e-6f;
-constexpr int kTileTok = 16;     // full-grid positions per CTA
+constexpr int kTileTok = 8;      // full-grid positions per CTA
 constexpr int kBThreads = 192;   // 4 channels per thread
 
 __device__ __forceinline__ float warp_sum2(float v) {
@@ -16,19 +16,84 @@ __device__ __forceinline__ float warp_sum2(float v) {
   return v;
 }
 
-// grid: B * (lens_full / 16).  Tile = 16 consecutive positions of one softmax domain (template
-// positions [0,64) or search positions [64,320): separate Prompt_block calls, vit_ce_prompt.py:212-213).
-//   p          = conv1x1( softmax_pos(x0*smooth) * x0 + x1 )          -> prompt stream P (all positions)
+// Fovea (vit_ce_prompt.py:33-47): per (sequence, domain) softmax over the domain's positions of
+// x0 * smooth, per channel; f = softmax * x0 + x1.  Domains: template positions [0,64), search
+// positions [64,320) -- separate Prompt_block calls (vit_ce_prompt.py:212-213, 301-302).  Removed
+// search positions take part in the normaliser (their x0 is conv0_0(beta)).
+// grid (B, 2), 256 threads: one position per thread.
+__global__ void __launch_bounds__(256)
+fovea_kernel(const float* __restrict__ xd, float smooth, float* __restrict__ F, int lens_t, int lens_full) {
+  __shared__ float s_red[8][8];
+  const int b = blockIdx.x, dom = blockIdx.y, t = threadIdx.x;
+  const int dom0 = dom == 0 ? 0 : lens_t;
+  const int domL = dom == 0 ? lens_t : lens_full - lens_t;
+  const int warp = t >> 5, lane = t & 31;
+  const bool act = t < domL;
+  float x0[8], x1[8], lg[8];
+  if (act) {
+    const float4* r = reinterpret_cast<const float4*>(xd + ((size_t)b * lens_full + dom0 + t) * 16);
+    const float4 a = r[0], c = r[1], d = r[2], e = r[3];
+    x0[0] = a.x; x0[1] = a.y; x0[2] = a.z; x0[3] = a.w; x0[4] = c.x; x0[5] = c.y; x0[6] = c.z; x0[7] = c.w;
+    x1[0] = d.x; x1[1] = d.y; x1[2] = d.z; x1[3] = d.w; x1[4] = e.x; x1[5] = e.y; x1[6] = e.z; x1[7] = e.w;
+  }
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    lg[k] = act ? x0[k] * smooth : -INFINITY;
+    float m = lg[k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if (lane == 0) s_red[warp][k] = m;
+  }
+  __syncthreads();
+  float mx[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    float m = s_red[0][k];
+#pragma unroll
+    for (int w = 1; w < 8; ++w) m = fmaxf(m, s_red[w][k]);
+    mx[k] = m;
+  }
+  __syncthreads();
+  float e[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    e[k] = act ? expf(lg[k] - mx[k]) : 0.f;
+    const float s = warp_sum2(e[k]);
+    if (lane == 0) s_red[warp][k] = s;
+  }
+  __syncthreads();
+  if (!act) return;
+  float f[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    float s = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) s += s_red[w][k];
+    f[k] = (e[k] / s) * x0[k] + x1[k];
+  }
+  float4* o = reinterpret_cast<float4*>(F + ((size_t)b * lens_full + dom0 + t) * 8);
+  o[0] = make_float4(f[0], f[1], f[2], f[3]);
+  o[1] = make_float4(f[4], f[5], f[6], f[7]);
+}
+
+int launch_fovea(const float* xd, float smooth, float* F, int B, int lens_t, int lens_full, cudaStream_t st) {
+  if (lens_t > 256 || lens_full - lens_t > 256) return VIPT_ERR_ARG;
+  fovea_kernel<<<dim3(B, 2), 256, 0, st>>>(xd, smooth, F, lens_t, lens_full);
+  return cudaGetLastError() == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
+}
+
+// Prompt phase B.  grid: B * (lens_full / 8); tile = 8 consecutive full-grid positions.
+//   p          = conv1x1(f)                                          -> prompt stream P (all positions)
 //   x[row]     = base[row] + p (+ pos_embed at layer 0)               -> kept positions only
 //   xn[row]    = LayerNorm_norm1(x[row]) in fp16                      -> feeds the qkv GEMM
-__global__ void __launch_bounds__(kBThreads)
-prompt_b_kernel(const float* __restrict__ xd, const float* __restrict__ w1, const float* __restrict__ b1, float smooth,
-                float* __restrict__ P, const float* base, float* x, int n_cur,   // base may alias x (in-place)
+// All 8 residual rows are loaded up front (independent 3 KB rows in flight), then streamed out.
+__global__ void __launch_bounds__(kBThreads, 3)
+prompt_b_kernel(const float* __restrict__ F, const float* __restrict__ w1, const float* __restrict__ b1,
+                float* __restrict__ P, const float* base, const op_t* __restrict__ delta, float* x,
+                int n_cur,   // base may alias x (in-place); delta = fp16 mlp.fc2 output still to be added
                 const int* __restrict__ slot_of_pos, const float* __restrict__ pos_embed,
                 const float* __restrict__ gamma1, const float* __restrict__ beta1, op_t* __restrict__ xn, int lens_t,
                 int lens_full) {
-  __shared__ float s_red[8][8];       // per-channel partial max / sum
-  __shared__ float s_max[8], s_inv[8];
   __shared__ float s_f[kTileTok][8];
   __shared__ float s_part[kTileTok][6][2];
   __shared__ int s_row[kTileTok];
@@ -36,41 +101,9 @@ prompt_b_kernel(const float* __restrict__ xd, const float* __restrict__ w1, cons
   const int tiles_per_b = lens_full / kTileTok;
   const int b = blockIdx.x / tiles_per_b;
   const int t0 = (blockIdx.x % tiles_per_b) * kTileTok;
-  const int dom0 = t0 < lens_t ? 0 : lens_t;
-  const int domL = t0 < lens_t ? lens_t : lens_full - lens_t;
-  const float* xd_b = xd + (size_t)b * lens_full * 16;
-
-  // ---- Fovea softmax statistics over the domain's positions, per channel (threads 0..63)
-  if (tid < 64) {
-    const int k = tid >> 3, sub = tid & 7;
-    float m = -INFINITY;
-    for (int p = sub; p < domL; p += 8) m = fmaxf(m, xd_b[(dom0 + p) * 16 + k] * smooth);
-    s_red[k][sub] = m;
-  }
-  __syncthreads();
-  if (tid < 8) {
-    float m = s_red[tid][0];
-#pragma unroll
-    for (int i = 1; i < 8; ++i) m = fmaxf(m, s_red[tid][i]);
-    s_max[tid] = m;
-  }
-  __syncthreads();
-  if (tid < 64) {
-    const int k = tid >> 3, sub = tid & 7;
-    const float m = s_max[k];
-    float s = 0.f;
-    for (int p = sub; p < domL; p += 8) s += expf(xd_b[(dom0 + p) * 16 + k] * smooth - m);
-    s_red[k][sub] = s;
-  }
-  __syncthreads();
-  if (tid < 8) {
-    float s = 0.f;
-#pragma unroll
-    for (int i = 0; i < 8; ++i) s += s_red[tid][i];
-    s_inv[tid] = 1.0f / s;
-  }
-  if (tid >= 64 && tid < 64 + kTileTok) {
-    const int tt = tid - 64, t = t0 + tt;
+  if (tid < kTileTok * 8) s_f[tid >> 3][tid & 7] = F[((size_t)b * lens_full + t0) * 8 + tid];
+  if (tid >= 128 && tid < 128 + kTileTok) {
+    const int tt = tid - 128, t = t0 + tt;
     int r = t;
     if (t >= lens_t && slot_of_pos) {
       const int s = slot_of_pos[b * (lens_full - lens_t) + (t - lens_t)];
@@ -79,16 +112,21 @@ prompt_b_kernel(const float* __restrict__ xd, const float* __restrict__ w1, cons
     s_row[tt] = r;
   }
   __syncthreads();
-  if (tid < kTileTok * 8) {
-    const int tt = tid >> 3, k = tid & 7;
-    const float x0 = xd_b[(t0 + tt) * 16 + k], x1 = xd_b[(t0 + tt) * 16 + 8 + k];
-    const float mask = expf(x0 * smooth - s_max[k]) * s_inv[k];
-    s_f[tt][k] = mask * x0 + x1;
-  }
-  __syncthreads();
 
-  // ---- up-projection: this thread owns channels c0..c0+3
   const int c0 = tid * 4;
+  float4 xv[kTileTok];
+#pragma unroll
+  for (int tt = 0; tt < kTileTok; ++tt) {
+    const int r = s_row[tt];
+    xv[tt] = r >= 0 ? *reinterpret_cast<const float4*>(base + ((size_t)b * n_cur + r) * D + c0)
+                    : make_float4(0.f, 0.f, 0.f, 0.f);
+    if (delta && r >= 0) {
+      const uint2 u = *reinterpret_cast<const uint2*>(delta + ((size_t)b * n_cur + r) * D + c0);
+      const float2 d0 = __half22float2(*reinterpret_cast<const __half2*>(&u.x));
+      const float2 d1 = __half22float2(*reinterpret_cast<const __half2*>(&u.y));
+      xv[tt].x += d0.x; xv[tt].y += d0.y; xv[tt].z += d1.x; xv[tt].w += d1.y;
+    }
+  }
   float w[4][8];
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
@@ -98,7 +136,6 @@ prompt_b_kernel(const float* __restrict__ xd, const float* __restrict__ w1, cons
     w[i][4] = hi.x; w[i][5] = hi.y; w[i][6] = hi.z; w[i][7] = hi.w;
   }
   const float4 bias = *reinterpret_cast<const float4*>(b1 + c0);
-  float4 xv[kTileTok];
   const int warp = tid >> 5, lane = tid & 31;
 #pragma unroll
   for (int tt = 0; tt < kTileTok; ++tt) {
@@ -112,9 +149,8 @@ prompt_b_kernel(const float* __restrict__ xd, const float* __restrict__ w1, cons
     const int t = t0 + tt;
     *reinterpret_cast<float4*>(P + ((size_t)b * lens_full + t) * D + c0) = make_float4(p[0], p[1], p[2], p[3]);
     const int r = s_row[tt];
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    float4 v = xv[tt];
     if (r >= 0) {
-      v = *reinterpret_cast<const float4*>(base + ((size_t)b * n_cur + r) * D + c0);
       v.x += p[0]; v.y += p[1]; v.z += p[2]; v.w += p[3];
       if (pos_embed) {
         const float4 pe = *reinterpret_cast<const float4*>(pos_embed + (size_t)t * D + c0);
@@ -157,10 +193,11 @@ prompt_b_kernel(const float* __restrict__ xd, const float* __restrict__ w1, cons
   }
 }
 
-int launch_prompt_b(const float* xd, const float* w1, const float* b1, float smooth, float* P, const float* base,
+int launch_prompt_b(const float* F, const float* w1, const float* b1, float* P, const float* base, const void* delta,
                     float* x, int n_cur, const int* slot_of_pos, const float* pos_embed, const float* gamma1,
                     const float* beta1, void* xn, int B, int lens_t, int lens_full, cudaStream_t st) {
-  prompt_b_kernel<<<B * (lens_full / kTileTok), kBThreads, 0, st>>>(xd, w1, b1, smooth, P, base, x, n_cur, slot_of_pos,
+  prompt_b_kernel<<<B * (lens_full / kTileTok), kBThreads, 0, st>>>(F, w1, b1, P, base, reinterpret_cast<const op_t*>(delta), x, n_cur,
+                                                                     slot_of_pos,
                                                                      pos_embed, gamma1, beta1,
                                                                      reinterpret_cast<op_t*>(xn), lens_t, lens_full);
   return cudaGetLastError() == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
@@ -220,7 +257,8 @@ int launch_ce_topk(const float* ce_prob, int n_heads, int n_s, int n_keep, const
 // (B, 320, 768), optional, is the `backbone_feat` the model API returns.
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-final_norm_kernel(const float* __restrict__ x, int n_cur, const int* __restrict__ slot_of_pos,
+final_norm_kernel(const float* __restrict__ x, const op_t* __restrict__ delta, int n_cur,
+                  const int* __restrict__ slot_of_pos,
                   const float* __restrict__ gamma, const float* __restrict__ beta, op_t* __restrict__ feat16,
                   float* __restrict__ feat32, int B, int lens_t, int lens_full) {
   const int lane = threadIdx.x & 31;
@@ -241,6 +279,12 @@ final_norm_kernel(const float* __restrict__ x, int n_cur, const int* __restrict_
 #pragma unroll
     for (int j = 0; j < 6; ++j) {
       v[j] = reinterpret_cast<const float4*>(src)[lane + 32 * j];
+      if (delta) {
+        const uint2 u = reinterpret_cast<const uint2*>(delta + ((size_t)b * n_cur + r) * D)[lane + 32 * j];
+        const float2 d0 = __half22float2(*reinterpret_cast<const __half2*>(&u.x));
+        const float2 d1 = __half22float2(*reinterpret_cast<const __half2*>(&u.y));
+        v[j].x += d0.x; v[j].y += d0.y; v[j].z += d1.x; v[j].w += d1.y;
+      }
       s += v[j].x + v[j].y + v[j].z + v[j].w;
     }
     const float mean = warp_sum2(s) * (1.0f / D);
@@ -276,10 +320,11 @@ final_norm_kernel(const float* __restrict__ x, int n_cur, const int* __restrict_
   }
 }
 
-int launch_final_norm(const float* x, int n_cur, const int* slot_of_pos, const float* gamma, const float* beta,
+int launch_final_norm(const float* x, const void* delta, int n_cur, const int* slot_of_pos, const float* gamma, const float* beta,
                       void* feat16, float* feat32, int B, int lens_t, int lens_full, cudaStream_t st) {
   const int rows = B * lens_full;
-  final_norm_kernel<<<(rows + 7) / 8, 256, 0, st>>>(x, n_cur, slot_of_pos, gamma, beta, reinterpret_cast<op_t*>(feat16),
+  final_norm_kernel<<<(rows + 7) / 8, 256, 0, st>>>(x, reinterpret_cast<const op_t*>(delta), n_cur, slot_of_pos, gamma, beta,
+                                                    reinterpret_cast<op_t*>(feat16),
                                                     feat32, B, lens_t, lens_full);
   return cudaGetLastError() == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
 }

@@ -45,6 +45,8 @@ rem = eng.buffer("removed").cpu()
 for i in range(3):
     a = rem[i, :, :nrem[i]].long(); b = ref["removed_indexes_s"][i]
     print("CE %d: set equal %s, order equal %s" % (i, [set(a[j].tolist()) == set(b[j].tolist()) for j in range(B)], torch.equal(a, b)))
+    from oracle import near_tie
+    print("   ref boundary gaps", near_tie.ce_boundary_gaps(ref)[i].tolist(), "diff tokens", [sorted(set(a[j].tolist()) ^ set(b[j].tolist())) for j in range(B)])
     sc = eng.buffer("ce_score").cpu()[i]
     rs = ref["ce_scores"][i]
     print("   ce score rel err", rel(sc[:, :rs.shape[1]], rs))

@@ -10,12 +10,11 @@ import numpy as np
 import pytest
 import torch
 
-from oracle import vipt_oracle as vo
+from oracle import near_tie, vipt_oracle as vo
 from vipt_b200 import synth
 from vipt_b200.model import build_viptrack
 
 pytestmark = pytest.mark.gpu
-TAU_CE = 1e-3
 CFG = {"MODEL": {"BACKBONE": {"TYPE": "vit_base_patch16_224_ce_prompt", "STRIDE": 16, "CE_LOC": [3, 6, 9],
                               "CE_KEEP_RATIO": [0.7, 0.7, 0.7], "CE_TEMPLATE_RANGE": "CTR_POINT"},
                  "HEAD": {"TYPE": "CENTER", "NUM_CHANNELS": 256}},
@@ -29,26 +28,10 @@ def _model(ptype):
     return m.cuda().eval()
 
 
-def check_ce_sets(removed_gpu, removed_ref, ce_scores_ref=None):
-    """sets equal, or every disagreeing token sits at a documented near-tie of the keep boundary."""
-    flips = 0
-    for i in range(3):
-        for b in range(removed_ref[i].shape[0]):
-            a = set(removed_gpu[i][b].tolist()); r = set(removed_ref[i][b].tolist())
-            if a == r:
-                continue
-            flips += 1
-            assert ce_scores_ref is not None, "CE set differs (stage %d, seq %d)" % (i, b)
-            sc = ce_scores_ref[i][b]
-            keep = sc.numel() - len(r)
-            srt = torch.sort(sc, descending=True).values
-            boundary = 0.5 * (srt[keep - 1] + srt[keep]).item()
-            # every slot whose fate differs must have a reference score within TAU_CE of the boundary
-            assert len(a ^ r) <= 4, "more than a boundary swap differs"
-            gap = (srt[keep - 1] - srt[keep]).item() / boundary
-            assert gap < TAU_CE, "CE set differs away from a near-tie (gap %.2e)" % gap
-            break   # later stages see different tokens once one stage flips
-    return flips
+def ce_status(out, ref_removed, ref_scores):
+    st = near_tie.ce_set_status([r.cpu() for r in out["removed_indexes_s"]], ref_removed, ref_scores)
+    assert "mismatch" not in st, st          # CE kept sets: bit-exact except at documented near-ties
+    return st
 
 
 @pytest.mark.parametrize("name,ptype", [("deep", "vipt_deep"), ("shaw", "vipt_shaw")])
@@ -63,19 +46,23 @@ def test_forward_matches_reference_golden(golden_dir, name, ptype):
     assert out["pred_boxes"].shape == (2, 1, 4) and out["score_map"].shape == (2, 1, 16, 16)
     assert out["size_map"].shape == (2, 2, 16, 16) and out["offset_map"].shape == (2, 2, 16, 16)
     assert [tuple(r.shape) for r in out["removed_indexes_s"]] == [(2, 76), (2, 54), (2, 37)]
-    flips = check_ce_sets([r.cpu() for r in out["removed_indexes_s"]],
-                          [torch.from_numpy(g[name + "_removed_%d" % i]) for i in range(3)])
-    assert flips == 0
+    with torch.no_grad():   # the pinned oracle supplies the reference CE scores for the near-tie criterion
+        orc = vo.model_forward(synth.synthetic_state_dict(ptype, 0), z, x, vo.ce_template_mask(2), ptype)
+    st = ce_status(out, [torch.from_numpy(g[name + "_removed_%d" % i]) for i in range(3)], orc["ce_scores"])
+    eq = [b for b in range(2) if st[b] == "equal"]
+    assert eq, "every sequence of the golden sits at a CE near-tie: %s" % st
     for k in ("score_map", "size_map", "offset_map"):
-        ref = torch.from_numpy(g[name + "_" + k])
-        err = (out[k].cpu() - ref).abs().max().item() / ref.abs().max().item()
+        ref = torch.from_numpy(g[name + "_" + k])[eq]
+        err = (out[k].cpu()[eq] - ref).abs().max().item() / ref.abs().max().item()
         assert err < 1e-2, (k, err)
-    ref_arg = torch.from_numpy(g[name + "_score_map"]).flatten(1).argmax(1)
-    assert torch.equal(out["score_map"].cpu().flatten(1).argmax(1), ref_arg)
-    box_px = (out["pred_boxes"].cpu() - torch.from_numpy(g[name + "_pred_boxes"])).abs().max().item() * 256
-    assert box_px < 0.5, box_px
+    ref_sm = torch.from_numpy(g[name + "_score_map"])
+    for b in eq:
+        if near_tie.argmax_gap(ref_sm[b:b + 1]).item() > near_tie.TAU_AM:
+            assert out["score_map"].cpu()[b].flatten().argmax() == ref_sm[b].flatten().argmax()
+            box_px = (out["pred_boxes"].cpu()[b] - torch.from_numpy(g[name + "_pred_boxes"])[b]).abs().max().item() * 256
+            assert box_px < 0.5, box_px
     feat = out["backbone_feat"].cpu()[:, ::16, ::32]
-    np.testing.assert_allclose(feat.numpy(), g[name + "_feat_sample"], atol=2e-2)
+    np.testing.assert_allclose(feat.numpy()[eq], g[name + "_feat_sample"][eq], atol=2e-2)
 
 
 def test_forward_batch_vs_oracle():
@@ -88,11 +75,14 @@ def test_forward_batch_vs_oracle():
     with torch.no_grad():
         ref = vo.model_forward(sd, z, x, mask, "vipt_deep")
     out = _model("vipt_deep").forward(z.cuda(), x.cuda(), mask.cuda())
-    flips = check_ce_sets([r.cpu() for r in out["removed_indexes_s"]], ref["removed_indexes_s"], ref["ce_scores"])
-    if flips == 0:
-        err = (out["score_map"].cpu() - ref["score_map"]).abs().max().item() / ref["score_map"].max().item()
-        assert err < 1e-2, err
-        assert (out["pred_boxes"].cpu().view(B, 4) - ref["pred_boxes"].view(B, 4)).abs().max().item() * 256 < 0.5
+    st = ce_status(out, ref["removed_indexes_s"], ref["ce_scores"])
+    eq = [b for b in range(B) if st[b] == "equal"]
+    assert len(eq) >= 2, st
+    err = (out["score_map"].cpu()[eq] - ref["score_map"][eq]).abs().max().item() / ref["score_map"][eq].max().item()
+    assert err < 1e-2, err
+    for b in eq:
+        if near_tie.argmax_gap(ref["score_map"][b:b + 1]).item() > near_tie.TAU_AM:
+            assert (out["pred_boxes"].cpu().view(B, 4)[b] - ref["pred_boxes"].view(B, 4)[b]).abs().max().item() * 256 < 0.5
 
 
 def test_api_errors():
