@@ -85,20 +85,16 @@ int Engine::finalize_buffers() {
                 (int64_t)M0 * 768, 0, b_pe, nullptr));
   for (int i = 0; i < kDepth; ++i) {
     const int Ma = B * n_tok[i], Mm = B * n_mlp[i];
-    RET(gemm_plan(&g_qkv[i], xn, 768, 0, L[i].w_qkv, 768, 0, 1, Ma, 2304, 768, 256, EPI_BIAS_F16, qkv, 2304, 0, 0,
-                  L[i].b_qkv, nullptr));
+    RET(gemm2_plan(&g_qkv[i], xn, 768, L[i].w_qkv, 768, Ma, 2304, 768, EPI_BIAS_F16, qkv, 2304, L[i].b_qkv));
     RET(attention_plan(&a_op[i], qkv, B, n_tok[i]));
     // proj / fc2 write their branch output as fp16 (dbuf); the residual add is fused into the next
     // LayerNorm / prompt kernel, where it is coalesced
-    RET(gemm_plan(&g_proj[i], att, 768, 0, L[i].w_proj, 768, 0, 1, Ma, 768, 768, 256, EPI_BIAS_F16, dbuf, 768, 0, 0,
-                  L[i].b_proj, nullptr));
-    RET(gemm_plan(&g_fc1[i], xn, 768, 0, L[i].w_fc1, 768, 0, 1, Mm, 3072, 768, 256, EPI_GELU_F16, hbuf, 3072, 0, 0,
-                  L[i].b_fc1, nullptr));
-    RET(gemm_plan(&g_fc2[i], hbuf, 3072, 0, L[i].w_fc2, 3072, 0, 1, Mm, 768, 3072, 256, EPI_BIAS_F16, dbuf, 768, 0,
-                  0, L[i].b_fc2, nullptr));
+    RET(gemm2_plan(&g_proj[i], att, 768, L[i].w_proj, 768, Ma, 768, 768, EPI_BIAS_F16, dbuf, 768, L[i].b_proj));
+    RET(gemm2_plan(&g_fc1[i], xn, 768, L[i].w_fc1, 768, Mm, 3072, 768, EPI_GELU_F16, hbuf, 3072, L[i].b_fc1));
+    RET(gemm2_plan(&g_fc2[i], hbuf, 3072, L[i].w_fc2, 3072, Mm, 768, 3072, EPI_BIAS_F16, dbuf, 768, L[i].b_fc2));
   }
   const int MH = B * kLensX;
-  RET(gemm_plan(&g_c1, a_col, 6912, 0, w_c1, 6912, 0, 1, MH, 768, 6912, 256, EPI_RELU_F16, h1, 768, 0, 0, b_c1, nullptr));
+  RET(gemm2_plan(&g_c1, a_col, 6912, w_c1, 6912, MH, 768, 6912, EPI_RELU_F16, h1, 768, b_c1));
   RET(gemm_plan(&g_c2, a_col, 2304, (int64_t)MH * 2304, w_c2, 2304, 128 * 2304, 3, MH, 128, 2304, 128, EPI_RELU_F16, h2,
                 384, 0, 128, b_c2, nullptr));
   RET(gemm_plan(&g_c3, a_col, 1152, (int64_t)MH * 1152, w_c3, 1152, 64 * 1152, 3, MH, 64, 1152, 64, EPI_RELU_F16, h3, 192,

@@ -27,7 +27,7 @@ struct GemmParams {
 };
 
 struct GemmOp {
-  CUtensorMap tmA, tmB;
+  CUtensorMap tmA, tmB, tmC;   // tmC: output map of the 2-CTA kernel's TMA-store epilogue
   GemmParams p;
   int bn, epi;
 };
@@ -37,6 +37,10 @@ int make_tmap_f16(CUtensorMap* out, const void* base, int rank, const uint64_t* 
 int gemm_plan(GemmOp* op, const void* A, int64_t lda, int64_t a_group_stride, const void* W, int64_t ldw,
               int64_t w_group_stride, int G, int M, int N, int K, int bn, int epi, void* out, int64_t ldc,
               int64_t out_group_stride, int64_t out_group_col, const float* bias, const float* resid);
-int gemm_launch(const GemmOp& op, int num_sms, cudaStream_t st);
+int gemm_launch(const GemmOp& op, int num_sms, cudaStream_t st);   // dispatches 2-CTA plans (bn == 512) to gemm2
+// 2-CTA (cta_group::2) kernel for large single-group GEMMs with N % 256 == 0 (gemm2.cu)
+int gemm2_plan(GemmOp* op, const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, int epi,
+               void* out, int64_t ldc, const float* bias);
+int gemm2_launch(const GemmOp& op, int num_sms, cudaStream_t st);
 
 }  // namespace vipt

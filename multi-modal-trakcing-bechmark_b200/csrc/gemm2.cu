@@ -1,0 +1,322 @@
+// 2-CTA (cta_group::2) variant of the persistent tcgen05 GEMM for the large linear layers.
+//
+// A CTA pair (cluster of 2, one TPC) computes a 256 x 256 output tile with ONE tcgen05.mma.cta_group::2
+// stream issued by the leader CTA: each CTA stages its own 128 rows of A and HALF of the weight tile
+// (128 of the 256 W rows); the tensor cores of both SMs read both halves.  Per CTA and k-block that is
+// 16 KB + 16 KB from L2 instead of 16 KB + 32 KB for the same 128 x 256 x 64 MACs -- the single-CTA
+// kernel (gemm.cu) is bound by L2 -> SM operand traffic (~10 TB/s), not by the tensor pipe.
+//
+// Protocol (per smem stage s, per TMEM accumulator buffer a):
+//   full[s]   (leader)   : leader producer arrives with expect_tx(2 x 32 KB); BOTH CTAs' TMA loads
+//                          complete_tx on the leader's barrier (.cta_group::2 TMA form)
+//   empty[s]  (each CTA) : tcgen05.commit multicast from the leader's MMA thread
+//   tfull[a]  (each CTA) : tcgen05.commit multicast after the last k-block
+//   tempty[a] (leader)   : 4 epilogue warps of each CTA arrive (peer: remote arrive through mapa)
+#include "gemm.h"
+#include "sm100_ptx.cuh"
+
+namespace vipt {
+
+namespace g2 {
+constexpr int BM = 128;            // rows per CTA (256 per pair)
+constexpr int BN = 256;            // columns per pair tile
+constexpr int BK = 64;
+constexpr int kStages = 5;
+constexpr int kSlabCols = 64;                        // epilogue slab: 128 rows x 64 fp16 = 16 KB, SW128
+constexpr int kSlabBytes = BM * kSlabCols * 2;
+constexpr int kABytes = BM * BK * 2;
+constexpr int kBBytes = (BN / 2) * BK * 2;
+constexpr int kStageBytes = kABytes + kBBytes;
+constexpr int kThreads = 256;
+constexpr int kSmemBytes = 1024 + kStages * kStageBytes + 2 * kSlabBytes + BN * 4 + (2 * kStages + 4) * 8 + 16;
+}  // namespace g2
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t mapa_cta(uint32_t local_addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// TMA load into this CTA's smem, completion signalled on a barrier that may live in the peer CTA
+__device__ __forceinline__ void tma_load_3d_2cta(void* smem_dst, const CUtensorMap* m, uint32_t bar_cluster_addr, int c0,
+                                                 int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], "
+      "[%2];"
+      ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(bar_cluster_addr), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+__device__ __forceinline__ void umma_f16_2cta(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                              uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}\n"
+      ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit_2cta(uint64_t* bar) {     // arrives on the barrier of BOTH CTAs
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+      ::"r"(smem_u32(bar)), "h"((uint16_t)3)
+      : "memory");
+}
+
+__device__ __forceinline__ float gelu_erf2(float x) {      // see gemm.cu
+  const float z = fabsf(x) * 0.70710678118654752f;
+  float t;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, z, 1.0f)));
+  float p = fmaf(1.061405429f, t, -1.453152027f);
+  p = fmaf(p, t, 1.421413741f);
+  p = fmaf(p, t, -0.284496736f);
+  p = fmaf(p, t, 0.254829592f);
+  float e;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-1.4426950408889634f * z * z));
+  const float erf_abs = fmaf(-p * t, e, 1.0f);
+  return 0.5f * x + 0.5f * fabsf(x) * erf_abs;
+}
+
+template <int EPI>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(g2::kThreads, 1)
+gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+             const __grid_constant__ CUtensorMap tmC, GemmParams p) {
+  using namespace g2;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* tiles = smem;
+  uint8_t* slab = smem + kStages * kStageBytes;            // 2 x 16 KB output staging (TMA store source)
+  float* bias_s = reinterpret_cast<float*>(slab + 2 * kSlabBytes);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(bias_s + BN);
+  uint64_t* empty_bar = full_bar + kStages;
+  uint64_t* tfull_bar = empty_bar + kStages;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int cluster_id = blockIdx.x >> 1;
+  const int num_clusters = gridDim.x >> 1;
+  const int tiles_m = (p.M + 2 * BM - 1) / (2 * BM);
+  const int tiles_n = p.N / BN;
+  const int num_tiles = tiles_m * tiles_n;
+  const int num_kb = p.K / BK;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    tma_prefetch_desc(&tmC);
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tfull_bar[a], 1);
+      mbar_init(&tempty_bar[a], 8);   // 4 epilogue warps x 2 CTAs (leader's copy is the one used)
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "n"(512)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  __syncwarp();
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();              // peer barriers are initialised before any remote arrive / multicast
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (threadIdx.x == 0) {
+    // ------------------------------------------------ TMA producer (both CTAs)
+    int s = 0;
+    uint32_t ph = 0;
+    for (int t = cluster_id; t < num_tiles; t += num_clusters) {
+      const int tn = t % tiles_n;
+      const int tm = t / tiles_n;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(&empty_bar[s], ph ^ 1);
+        uint8_t* a_dst = tiles + s * kStageBytes;
+        uint8_t* b_dst = a_dst + kABytes;
+        if (leader) mbar_expect_tx(&full_bar[s], 2 * kStageBytes);
+        const uint32_t bar = mapa_cta(smem_u32(&full_bar[s]), 0);
+        tma_load_3d_2cta(a_dst, &tmA, bar, kb * BK, tm * 2 * BM + (int)rank * BM, 0);
+        tma_load_3d_2cta(b_dst, &tmB, bar, kb * BK, tn * BN + (int)rank * (BN / 2), 0);
+        if (++s == kStages) { s = 0; ph ^= 1; }
+      }
+    }
+  } else if (threadIdx.x == 32 && leader) {
+    // ------------------------------------------------ MMA issuer (leader CTA only)
+    constexpr uint32_t idesc = make_idesc(2 * BM, BN);
+    int s = 0;
+    uint32_t ph = 0;
+    int as = 0;
+    uint32_t aph = 0;
+    for (int t = cluster_id; t < num_tiles; t += num_clusters) {
+      mbar_wait(&tempty_bar[as], aph ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + as * BN;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(&full_bar[s], ph);
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(tiles + s * kStageBytes);
+        const uint64_t adesc = make_sdesc_sw128(a_addr);
+        const uint64_t bdesc = make_sdesc_sw128(a_addr + kABytes);
+#pragma unroll
+        for (int k = 0; k < BK / 16; ++k) umma_f16_2cta(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+        umma_commit_2cta(&empty_bar[s]);
+        if (++s == kStages) { s = 0; ph ^= 1; }
+      }
+      umma_commit_2cta(&tfull_bar[as]);
+      if (++as == 2) { as = 0; aph ^= 1; }
+    }
+  } else if (warp >= 4) {
+    // ------------------------------------------------ epilogue (both CTAs, own 128 rows)
+    const int we = warp - 4;
+    const int et = threadIdx.x - 128;
+    int as = 0;
+    uint32_t aph = 0;
+    for (int t = cluster_id; t < num_tiles; t += num_clusters) {
+      const int tn = t % tiles_n;
+      const int tm = t / tiles_n;
+      const int n0 = tn * BN;
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      for (int i = et; i < BN; i += 128) bias_s[i] = p.bias ? p.bias[n0 + i] : 0.f;
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      mbar_wait(&tfull_bar[as], aph);
+      tc_fence_after();
+      const int row0 = tm * 2 * BM + (int)rank * BM;           // first row of this CTA's 128 x 256 tile
+      const int r = we * 32 + lane;                            // row within the tile == TMEM lane
+#pragma unroll 1
+      for (int sl = 0; sl < BN / kSlabCols; ++sl) {
+        uint32_t v0[32], v1[32];
+        const uint32_t taddr = tmem_base + as * BN + sl * kSlabCols + ((uint32_t)(we * 32) << 16);
+        tmem_ld32(taddr, v0);
+        tmem_ld32(taddr + 32, v1);
+        uint8_t* buf = slab + (sl & 1) * kSlabBytes;
+        // the TMA store that last read this staging buffer (two slabs ago) must have drained it
+        if (et == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        tmem_ld_wait();
+        uint8_t* prow = buf + r * 128;
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+          float f[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            f[j] = __uint_as_float(hh == 0 ? v0[j] : v1[j]) + bias_s[sl * kSlabCols + hh * 32 + j];
+          if (EPI == EPI_GELU_F16) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] = gelu_erf2(f[j]);
+          }
+          if (EPI == EPI_RELU_F16) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+          }
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            uint4 u;
+            u.x = pack_op2(f[q * 8 + 0], f[q * 8 + 1]);
+            u.y = pack_op2(f[q * 8 + 2], f[q * 8 + 3]);
+            u.z = pack_op2(f[q * 8 + 4], f[q * 8 + 5]);
+            u.w = pack_op2(f[q * 8 + 6], f[q * 8 + 7]);
+            const int chunk = (hh * 4 + q) ^ (r & 7);          // 128-byte swizzle, matches tmC
+            *reinterpret_cast<uint4*>(prow + chunk * 16) = u;
+          }
+        }
+        fence_proxy_async_smem();
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (et == 0) {
+          asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+                       ::"l"(reinterpret_cast<uint64_t>(&tmC)), "r"(smem_u32(buf)), "r"(n0 + sl * kSlabCols), "r"(row0),
+                       "r"(0)
+                       : "memory");
+          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(mapa_cta(smem_u32(&tempty_bar[as]), 0));
+      if (++as == 2) { as = 0; aph ^= 1; }
+    }
+  }
+  if (threadIdx.x == 128) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // staging smem drained
+  __syncwarp();
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();              // neither CTA may exit / free TMEM while the pair is still in flight
+  if (warp == 2) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(512) : "memory");
+  }
+}
+
+template <int EPI>
+static int launch2_t(const GemmOp& op, int num_sms, cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    if (cudaFuncSetAttribute(gemm2_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, g2::kSmemBytes) != cudaSuccess)
+      return VIPT_ERR_LAUNCH;
+    attr_set = true;
+  }
+  const int tiles = ((op.p.M + 255) / 256) * (op.p.N / 256);
+  int grid = 2 * tiles;
+  const int cap = num_sms & ~1;
+  if (grid > cap) grid = cap;
+  gemm2_kernel<EPI><<<grid, g2::kThreads, g2::kSmemBytes, st>>>(op.tmA, op.tmB, op.tmC, op.p);
+  return cudaGetLastError() == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
+}
+
+int gemm2_launch(const GemmOp& op, int num_sms, cudaStream_t st) {
+  switch (op.epi) {
+    case EPI_BIAS_F16: return launch2_t<EPI_BIAS_F16>(op, num_sms, st);
+    case EPI_GELU_F16: return launch2_t<EPI_GELU_F16>(op, num_sms, st);
+    case EPI_RELU_F16: return launch2_t<EPI_RELU_F16>(op, num_sms, st);
+  }
+  return VIPT_ERR_ARG;
+}
+
+// same operand conventions as gemm_plan, single group, N % 256 == 0; W box = 128 rows (half tile per CTA)
+int gemm2_plan(GemmOp* op, const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, int epi,
+               void* out, int64_t ldc, const float* bias) {
+  if (K % g2::BK != 0 || N % g2::BN != 0 || M <= 0 || epi == EPI_RESID_F32 || epi == EPI_BIAS_F32) return VIPT_ERR_ARG;
+  if ((ldc * 2) % 16 != 0 || (reinterpret_cast<uintptr_t>(out) & 15)) return VIPT_ERR_ARG;
+  if ((lda * 2) % 16 != 0 || (ldw * 2) % 16 != 0 || (reinterpret_cast<uintptr_t>(A) & 15) ||
+      (reinterpret_cast<uintptr_t>(W) & 15))
+    return VIPT_ERR_ARG;
+  uint64_t da[3] = {(uint64_t)K, (uint64_t)M, 1};
+  uint64_t sa[2] = {(uint64_t)lda * 2, (uint64_t)M * lda * 2};
+  uint32_t ba[3] = {g2::BK, g2::BM, 1};
+  int r = make_tmap_f16(&op->tmA, A, 3, da, sa, ba);
+  if (r) return r;
+  uint64_t db[3] = {(uint64_t)K, (uint64_t)N, 1};
+  uint64_t sb[2] = {(uint64_t)ldw * 2, (uint64_t)N * ldw * 2};
+  uint32_t bb[3] = {g2::BK, g2::BN / 2, 1};
+  r = make_tmap_f16(&op->tmB, W, 3, db, sb, bb);
+  if (r) return r;
+  uint64_t dc[3] = {(uint64_t)N, (uint64_t)M, 1};
+  uint64_t sc[2] = {(uint64_t)ldc * 2, (uint64_t)M * ldc * 2};
+  uint32_t bc[3] = {g2::kSlabCols, g2::BM, 1};
+  r = make_tmap_f16(&op->tmC, out, 3, dc, sc, bc);
+  if (r) return r;
+  op->p.M = M; op->p.N = N; op->p.K = K; op->p.G = 1;
+  op->p.out = out; op->p.ldc = ldc; op->p.out_group_stride = 0; op->p.out_group_col = 0;
+  op->p.bias = bias; op->p.resid = nullptr;
+  op->bn = 512;      // marks a 2-CTA plan
+  op->epi = epi;
+  return VIPT_OK;
+}
+
+}  // namespace vipt

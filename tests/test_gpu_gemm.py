@@ -21,6 +21,8 @@ def _ref(A, W, bias, epi, resid):
 @pytest.mark.parametrize("M,N,K,bn,epi", [
     (128, 256, 64, 256, 3), (128, 256, 128, 256, 3), (256, 256, 768, 256, 3),
     (320, 768, 768, 256, 0), (1000, 2304, 768, 256, 0), (777, 3072, 768, 256, 1), (640, 768, 3072, 256, 4),
+    (256, 256, 64, 512, 0), (256, 256, 768, 512, 0), (1000, 2304, 768, 512, 0), (777, 3072, 768, 512, 1),
+    (20480, 768, 3072, 512, 0), (9792, 768, 768, 512, 2), (130, 256, 128, 512, 1),
     (500, 128, 2304, 128, 2), (300, 64, 1152, 64, 2), (260, 32, 576, 32, 2), (20480, 768, 768, 256, 4),
 ])
 def test_gemm(M, N, K, bn, epi):
