@@ -120,8 +120,8 @@ int vipt_engine_buffer(void* ev, const char* name, void** ptr, int64_t* bytes) {
       {"score_map", e->score_map, RH * 4}, {"size_map", e->size_map, 2 * RH * 4}, {"offset_map", e->offset_map, 2 * RH * 4},
       {"pred_boxes", e->pred_boxes, e->B * 16}, {"removed", e->removed, 3 * RH * 4}, {"ce_score", e->ce_score, 3 * RH * 4},
       {"feat32", e->feat32, R * 768 * 4}, {"feat16", e->feat16, RH * 768 * 2}, {"x", e->x_final ? e->x_final : e->xA, R * 768 * 4},
-      {"xA", e->xA, R * 768 * 4}, {"xB", e->xB, R * 768 * 4}, {"xn", e->xn, R * 768 * 2}, {"dbuf", e->dbuf, R * 768 * 2}, {"P", e->P, R * 768 * 4},
-      {"XD", e->XD, R * 16 * 4}, {"E", e->E, 2 * R * 768 * 4}, {"qkv", e->qkv, R * 2304 * 2}, {"att", e->att, R * 768 * 2},
+      {"xA", e->xA, R * 768 * 4}, {"xB", e->xB, R * 768 * 4}, {"xn", e->xn, R * 768 * 2}, {"dbuf", e->dbuf, R * 768 * 2},
+      {"XD", e->XD, R * 16 * 4}, {"FV", e->FV, R * 8 * 4}, {"E", e->E, 2 * R * 768 * 4}, {"qkv", e->qkv, R * 2304 * 2}, {"att", e->att, R * 768 * 2},
       {"hbuf", e->hbuf, R * 3072 * 2}, {"gi", e->gi_final ? e->gi_final : e->giA, RH * 4}, {"slot_of_pos", e->slot_of_pos, RH * 4},
       {"h1", e->h1, RH * 768 * 2}, {"h4", e->h4, RH * 96 * 2}, {"state", e->state, e->B * 32}, {"out_boxes", e->out_boxes, e->B * 32},
       {"out_scores", e->out_scores, e->B * 4}, {"geom_x", e->geom_x, e->B * 32}, {"geom_z", e->geom_z, e->B * 32},

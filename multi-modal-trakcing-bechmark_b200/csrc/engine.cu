@@ -167,6 +167,53 @@ int Engine::finalize(int batch, bool deep_prompt) {
     PW[i].w1 = pk.up_f32(pk.get(p + "conv1x1.weight", 768 * 8)->data(), 768 * 8);
     PW[i].b1 = pk.up_f32(pk.get(p + "conv1x1.bias", 768)->data(), 768);
     PW[i].smooth = (*pk.get(p + "fovea.smooth", 1))[0];
+    PW[i].fold = nullptr; PW[i].w1t = nullptr;
+    if (i >= 1) {
+      // fused deep-prompt kernel (prompt_fused.cu): conv1x1 transposed to k-major, and the previous
+      // prompt P = W1p f + b1p (rank 8) folded through prompt_norms[i] and conv0_1 of this block.
+      const auto& w1 = *pk.get(p + "conv1x1.weight", 768 * 8);
+      std::vector<float> w1t(8 * 768);
+      for (int c = 0; c < 768; ++c)
+        for (int k = 0; k < 8; ++k) w1t[k * 768 + c] = w1[c * 8 + k];
+      PW[i].w1t = pk.up_f32(w1t.data(), w1t.size());
+      const std::string pp = bb + "prompt_blocks." + std::to_string(i - 1) + ".";
+      const auto& w1p = *pk.get(pp + "conv1x1.weight", 768 * 8);
+      const auto& b1p = *pk.get(pp + "conv1x1.bias", 768);
+      double m[8] = {0}, m0 = 0;
+      for (int c = 0; c < 768; ++c) {
+        for (int k = 0; k < 8; ++k) m[k] += (double)w1p[c * 8 + k];
+        m0 += (double)b1p[c];
+      }
+      for (int k = 0; k < 8; ++k) m[k] /= 768.0;
+      m0 /= 768.0;
+      double G[64] = {0}, h[8] = {0}, c0 = 0, A[64] = {0}, a0[8] = {0};
+      for (int c = 0; c < 768; ++c) {
+        double wc[8];
+        for (int k = 0; k < 8; ++k) wc[k] = (double)w1p[c * 8 + k] - m[k];
+        const double bc = (double)b1p[c] - m0;
+        for (int a = 0; a < 8; ++a) {
+          for (int q = 0; q < 8; ++q) G[a * 8 + q] += wc[a] * wc[q];
+          h[a] += wc[a] * bc;
+        }
+        c0 += bc * bc;
+        for (int k = 0; k < 8; ++k) {
+          const double wg = (double)w01[k * 768 + c] * (double)gd[c];
+          for (int q = 0; q < 8; ++q) A[k * 8 + q] += wg * wc[q];
+          a0[k] += wg * bc;
+        }
+      }
+      std::vector<float> fold(168, 0.f);
+      for (int k = 0; k < 8; ++k) {
+        fold[0 + k] = sc[8 + k];            // c_a = conv0_0(beta_a) + bias
+        fold[72 + k] = (float)a0[k];
+        fold[80 + k] = sc[24 + k];          // c_d = conv0_1(beta_d) + bias
+        fold[152 + k] = (float)(h[k] / 768.0);
+      }
+      for (int q = 0; q < 64; ++q) { fold[8 + q] = (float)A[q]; fold[88 + q] = (float)(G[q] / 768.0); }
+      fold[160] = (float)(c0 / 768.0);
+      fold[161] = PW[i].smooth;
+      PW[i].fold = pk.up_f32(fold.data(), fold.size());
+    }
   }
   // ---- center head: towers ctr | offset | size; BN folded
   {

@@ -27,6 +27,7 @@ struct LayerW {
 };
 struct PromptW {
   float *wg_a, *wg_d, *sc, *w1, *b1;
+  float *fold, *w1t;     // layers >= 1: folded rank-8 algebra + k-major conv1x1 of the fused kernel
   float smooth;
 };
 
@@ -56,7 +57,7 @@ struct Engine {
 
   // activations
   __half *apatch, *xn, *dbuf, *qkv, *att, *hbuf, *feat16, *a_col, *h1, *h2, *h3, *h4;
-  float *E, *xA, *xB, *P, *XD, *FV, *ce_prob, *ce_score, *feat32;
+  float *E, *xA, *xB, *XD, *FV, *ce_prob, *ce_score, *feat32;
   int *giA, *giB, *perm, *removed, *slot_of_pos, *ident, *err;
   // outputs / state
   float *score_map, *size_map, *offset_map, *pred_boxes, *out_scores;

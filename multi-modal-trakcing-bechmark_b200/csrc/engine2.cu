@@ -56,7 +56,7 @@ int Engine::finalize_buffers() {
   } while (0)
   AL(apatch, __half, 2 * R * 768);
   AL(E, float, 2 * R * 768);
-  AL(xA, float, R * 768); AL(xB, float, R * 768); AL(P, float, R * 768);
+  AL(xA, float, R * 768); AL(xB, float, R * 768);
   AL(XD, float, R * 16); AL(FV, float, R * 8);
   AL(xn, __half, R * 768); AL(dbuf, __half, R * 768); AL(qkv, __half, R * 2304); AL(att, __half, R * 768); AL(hbuf, __half, R * 3072);
   AL(ce_prob, float, (size_t)B * kHeads * kLensX); AL(ce_score, float, 3 * RH);
@@ -131,7 +131,7 @@ int Engine::run_backbone_head(bool tracking, bool want_feat32, int debug_stop, c
   const float* E1 = E + (size_t)B * kLensFull * 768;
   LAUNCH(K_PROMPT, launch_prompt_a(E0, nullptr, kLensFull, nullptr, E1, PW[0].wg_a, PW[0].wg_d, PW[0].sc, XD, B, kLensT, kLensFull, st));
   LAUNCH(K_PROMPT, launch_fovea(XD, PW[0].smooth, FV, B, kLensT, kLensFull, st));
-  LAUNCH(K_PROMPT, launch_prompt_b(FV, PW[0].w1, PW[0].b1, P, E0, nullptr, xA, kLensFull, nullptr, pos_embed, L[0].ln1_g,
+  LAUNCH(K_PROMPT, launch_prompt_b(FV, PW[0].w1, PW[0].b1, nullptr, E0, nullptr, xA, kLensFull, nullptr, pos_embed, L[0].ln1_g,
                       L[0].ln1_b, xn, B, kLensT, kLensFull, st));
   STAGE_END();   // 2: x, xn, P after the input prompt
   float* x = xA;
@@ -143,10 +143,8 @@ int Engine::run_backbone_head(bool tracking, bool want_feat32, int debug_stop, c
     const int n = n_tok[i];
     if (i >= 1) {
       if (deep) {
-        LAUNCH(K_PROMPT, launch_prompt_a(x, dbuf, n, slot_of_pos, P, PW[i].wg_a, PW[i].wg_d, PW[i].sc, XD, B, kLensT, kLensFull, st));
-        LAUNCH(K_PROMPT, launch_fovea(XD, PW[i].smooth, FV, B, kLensT, kLensFull, st));
-        LAUNCH(K_PROMPT, launch_prompt_b(FV, PW[i].w1, PW[i].b1, P, x, dbuf, x, n, slot_of_pos, nullptr, L[i].ln1_g,
-                            L[i].ln1_b, xn, B, kLensT, kLensFull, st));
+        LAUNCH(K_PROMPT, launch_prompt_fused(x, dbuf, n, gi, FV, PW[i].wg_a, PW[i].fold, PW[i].w1t, PW[i].b1, L[i].ln1_g,
+                                             L[i].ln1_b, xn, B, kLensT, kLensFull, st));
       } else {
         LAUNCH(K_NORM, launch_ln_rows(x, n, dbuf, nullptr, 0, x, xn, L[i].ln1_g, L[i].ln1_b, B, n, kLensT, st));
       }

@@ -147,7 +147,7 @@ prompt_b_kernel(const float* __restrict__ F, const float* __restrict__ w1, const
       for (int i = 0; i < 4; ++i) p[i] += w[i][k] * f;
     }
     const int t = t0 + tt;
-    *reinterpret_cast<float4*>(P + ((size_t)b * lens_full + t) * D + c0) = make_float4(p[0], p[1], p[2], p[3]);
+    if (P) *reinterpret_cast<float4*>(P + ((size_t)b * lens_full + t) * D + c0) = make_float4(p[0], p[1], p[2], p[3]);
     const int r = s_row[tt];
     float4 v = xv[tt];
     if (r >= 0) {

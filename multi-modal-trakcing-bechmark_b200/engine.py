@@ -13,7 +13,7 @@ _DTYPES = {
     "removed": (torch.int32, (3, -1, 256)), "ce_score": (torch.float32, (3, -1, 256)),
     "feat32": (torch.float32, (-1, 320, 768)), "feat16": (torch.float16, (-1, 256, 768)),
     "x": (torch.float32, None), "xA": (torch.float32, None), "xB": (torch.float32, None), "xn": (torch.float16, None), "dbuf": (torch.float16, None),
-    "P": (torch.float32, (-1, 320, 768)), "XD": (torch.float32, (-1, 320, 16)), "E": (torch.float32, (2, -1, 320, 768)),
+    "FV": (torch.float32, (-1, 320, 8)), "XD": (torch.float32, (-1, 320, 16)), "E": (torch.float32, (2, -1, 320, 768)),
     "qkv": (torch.float16, None), "att": (torch.float16, None), "hbuf": (torch.float16, None),
     "gi": (torch.int32, (-1, 256)), "slot_of_pos": (torch.int32, (-1, 256)), "perm": (torch.int32, (-1, 256)),
     "h1": (torch.float16, (-1, 256, 768)), "h4": (torch.float16, (-1, 256, 96)),
