@@ -29,6 +29,9 @@ SIGNATURES = {
     "vipt_engine_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]),
     "vipt_engine_init": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "vipt_engine_track_enqueue": (c_int, [c_void_p, c_void_p, c_int, c_void_p]),
+    "vipt_engine_init_host": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "vipt_engine_track_host": (c_int, [c_void_p, c_void_p, c_int, ctypes.POINTER(c_i64), c_void_p]),
+    "vipt_engine_set_state": (c_int, [c_void_p, c_void_p, c_void_p]),
     "vipt_engine_profile_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "vipt_engine_results": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),
     "vipt_engine_info": (c_i64, [c_void_p, ctypes.c_char_p]),

@@ -101,7 +101,24 @@ int vipt_engine_results(void* ev, double* boxes_host, float* scores_host, void* 
     return VIPT_ERR_LAUNCH;
   }
   if (herr == VIPT_ERR_SMALL_BOX) set_err("Too small bounding box.");
+  e->host_state.assign(boxes_host, boxes_host + 4 * e->B);     // mirror for the ROI uploads (engine3.cu)
+  e->mirror_valid = true;
   return herr;
+}
+int vipt_engine_init_host(void* e, const void* const* host_frames, const int* hw_host, const double* boxes_host,
+                          void* stream) {
+  if (!e || !host_frames || !hw_host || !boxes_host) return VIPT_ERR_ARG;
+  int r = ((vipt::Engine*)e)->init_host(host_frames, hw_host, boxes_host, (cudaStream_t)stream);
+  if (r == VIPT_ERR_SMALL_BOX) set_err("Too small bounding box.");
+  return r;
+}
+int vipt_engine_track_host(void* e, const void* const* host_frames, int use_graph, int64_t* bytes_copied, void* stream) {
+  if (!e || !host_frames) return VIPT_ERR_ARG;
+  return ((vipt::Engine*)e)->track_host(host_frames, use_graph != 0, bytes_copied, (cudaStream_t)stream);
+}
+int vipt_engine_set_state(void* e, const double* boxes_host, void* stream) {
+  if (!e || !boxes_host) return VIPT_ERR_ARG;
+  return ((vipt::Engine*)e)->set_state(boxes_host, (cudaStream_t)stream);
 }
 int64_t vipt_engine_info(void* ev, const char* what) {
   vipt::Engine* e = (vipt::Engine*)ev;

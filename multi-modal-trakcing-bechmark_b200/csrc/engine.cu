@@ -29,6 +29,7 @@ namespace vipt {
 Engine::~Engine() {
   if (graph_exec) cudaGraphExecDestroy(graph_exec);
   for (void* p : allocs) cudaFree(p);
+  for (void* p : own_frames) cudaFree(p);
 }
 
 void* Engine::dalloc(size_t bytes) {

@@ -74,6 +74,16 @@ struct Engine {
   float* x_final = nullptr;   // residual stream / index list after the last block (debug, forward outputs)
   int* gi_final = nullptr;
 
+  // host-frame path (engine3.cu): engine-owned frame buffers + host mirror of the box state
+  std::vector<void*> own_frames;
+  const uint8_t** own_ptrs_dev = nullptr;
+  std::vector<int> host_hw;
+  std::vector<double> host_state;
+  bool mirror_valid = false;
+  int init_host(const void* const* host_frames, const int* hw_host, const double* boxes_host, cudaStream_t st);
+  int track_host(const void* const* host_frames, bool use_graph, int64_t* bytes_copied, cudaStream_t st);
+  int set_state(const double* boxes_host, cudaStream_t st);
+
   // CUDA graph of one tracking step
   cudaGraphExec_t graph_exec = nullptr;
   long launches_per_step = 0;

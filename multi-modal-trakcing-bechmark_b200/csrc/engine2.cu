@@ -211,6 +211,8 @@ int Engine::init_sequences(const void* const* frames_host_ptrs, const int* hw_ho
   CK(cudaMemcpyAsync(frame_ptrs, frames_host_ptrs, sizeof(void*) * B, cudaMemcpyHostToDevice, st));
   CK(cudaMemcpyAsync(frame_hw, hw_host, sizeof(int) * 2 * B, cudaMemcpyHostToDevice, st));
   CK(cudaMemcpyAsync(state, boxes_host, sizeof(double) * 4 * B, cudaMemcpyHostToDevice, st));
+  host_state.assign(boxes_host, boxes_host + 4 * B);
+  mirror_valid = true;
   CK(cudaMemsetAsync(err, 0, 4, st));
   const int64_t gs = (int64_t)B * kLensFull * 768;
   // template: factor 2.0 -> 128 x 128 (vipt.py:43-48); the crop is kept as the resident patch rows 0..63

@@ -104,6 +104,29 @@ class NativeEngine:
         _lib.check(self.L.vipt_engine_init(self.h, ptrs, hw.ctypes.data_as(ctypes.c_void_p),
                                            bx.ctypes.data_as(ctypes.c_void_p), self._sp()), "vipt_engine_init")
 
+    def init_sequences_host(self, host_ptrs, hw, boxes, keepalive=None):
+        """host_ptrs: B host addresses of uint8 (H,W,6) frames; hw (B,2) int32; boxes (B,4)."""
+        self._frames_keepalive = keepalive
+        ptrs = (ctypes.c_void_p * self.batch)(*host_ptrs)
+        hw = np.ascontiguousarray(np.asarray(hw, np.int32).reshape(self.batch, 2))
+        bx = np.ascontiguousarray(np.asarray(boxes, np.float64).reshape(self.batch, 4))
+        _lib.check(self.L.vipt_engine_init_host(self.h, ptrs, hw.ctypes.data_as(ctypes.c_void_p),
+                                                bx.ctypes.data_as(ctypes.c_void_p), self._sp()), "vipt_engine_init_host")
+
+    def track_host(self, host_ptrs, use_graph=True, keepalive=None):
+        """Upload the search rectangles of B host frames and enqueue one step; returns bytes uploaded."""
+        self._frames_keepalive = keepalive
+        ptrs = (ctypes.c_void_p * self.batch)(*host_ptrs)
+        n = ctypes.c_int64(0)
+        _lib.check(self.L.vipt_engine_track_host(self.h, ptrs, int(use_graph), ctypes.byref(n), self._sp()),
+                   "vipt_engine_track_host")
+        return n.value
+
+    def set_state(self, boxes):
+        bx = np.ascontiguousarray(np.asarray(boxes, np.float64).reshape(self.batch, 4))
+        _lib.check(self.L.vipt_engine_set_state(self.h, bx.ctypes.data_as(ctypes.c_void_p), self._sp()),
+                   "vipt_engine_set_state")
+
     def track_enqueue(self, frame_ptrs_dev, use_graph=True):
         """frame_ptrs_dev: int64 CUDA tensor of B frame device pointers.  Asynchronous."""
         _lib.check(self.L.vipt_engine_track_enqueue(self.h, _lib.ptr(frame_ptrs_dev), int(use_graph), self._sp()),

@@ -34,35 +34,58 @@ class BatchedViPTTracker:
         self.frame_id = 0
         self._dev_frames = None
         self._ptrs = None
+        self._host_mode = False
+        self.h2d_bytes = 0
 
-    def _upload(self, images):
-        """host uint8 frames -> device (pinned staging, async copy); returns device tensors."""
-        out = []
-        with torch.cuda.stream(self.engine.stream):
-            for im in images:
-                if isinstance(im, torch.Tensor) and im.is_cuda:
-                    out.append(im)
-                else:
-                    t = torch.from_numpy(np.ascontiguousarray(im)) if not isinstance(im, torch.Tensor) else im
-                    assert t.dtype == torch.uint8 and t.dim() == 3 and t.shape[2] == 6, "frames are uint8 (H, W, 6)"
-                    if not t.is_pinned():
-                        t = t.pin_memory()
-                    out.append(t.to(self.engine.device, non_blocking=True))
-        return out
+    @staticmethod
+    def _is_host(im):
+        return isinstance(im, np.ndarray) or (isinstance(im, torch.Tensor) and not im.is_cuda)
+
+    @staticmethod
+    def _host_view(im):
+        """-> (address, (H, W), object to keep alive) of a host uint8 (H, W, 6) frame."""
+        if isinstance(im, np.ndarray):
+            a = np.ascontiguousarray(im)
+            assert a.dtype == np.uint8 and a.ndim == 3 and a.shape[2] == 6, "frames are uint8 (H, W, 6)"
+            return a.ctypes.data, a.shape[:2], a
+        t = im.contiguous()
+        assert t.dtype == torch.uint8 and t.dim() == 3 and t.shape[2] == 6, "frames are uint8 (H, W, 6)"
+        return t.data_ptr(), tuple(t.shape[:2]), t
 
     def initialize(self, images, init_boxes):
-        frames = self._upload(images)
-        self.engine.init_sequences(frames, np.asarray(init_boxes, np.float64))
+        boxes = np.asarray(init_boxes, np.float64).reshape(self.batch, 4)
+        self._host_mode = all(self._is_host(im) for im in images)
+        if self._host_mode:
+            views = [self._host_view(im) for im in images]
+            self._hw = [v[1] for v in views]
+            self.engine.init_sequences_host([v[0] for v in views], self._hw, boxes, keepalive=[v[2] for v in views])
+        else:
+            frames = [im if (isinstance(im, torch.Tensor) and im.is_cuda) else
+                      torch.from_numpy(np.ascontiguousarray(im)).to(self.engine.device) for im in images]
+            self.engine.init_sequences(frames, boxes)
         self.frame_id = 0
-        self.state = np.asarray(init_boxes, np.float64).reshape(self.batch, 4).copy()
+        self.state = boxes.copy()
+        self.h2d_bytes = 0
+
+    def set_state(self, boxes):
+        """Override the box state of every sequence (teacher-forced evaluation)."""
+        self.engine.set_state(boxes)
+        self.state = np.asarray(boxes, np.float64).reshape(self.batch, 4).copy()
 
     def track_async(self, images):
-        frames = self._upload(images)
-        with torch.cuda.stream(self.engine.stream):
-            ptrs = torch.tensor([f.data_ptr() for f in frames], dtype=torch.int64).pin_memory().to(
-                self.engine.device, non_blocking=True)
-        self._dev_frames, self._ptrs = frames, ptrs        # keep alive until the step has run
-        self.engine.track_enqueue(ptrs, self.use_graph)
+        if self._host_mode and all(self._is_host(im) for im in images):
+            views = [self._host_view(im) for im in images]
+            assert [v[1] for v in views] == self._hw, "frame size changed within a sequence"
+            # only the rectangle the search crop reads travels to the device (csrc/engine3.cu)
+            self.h2d_bytes = self.engine.track_host([v[0] for v in views], self.use_graph, keepalive=[v[2] for v in views])
+        else:
+            frames = [im if (isinstance(im, torch.Tensor) and im.is_cuda) else
+                      torch.from_numpy(np.ascontiguousarray(im)).to(self.engine.device) for im in images]
+            with torch.cuda.stream(self.engine.stream):
+                ptrs = torch.tensor([f.data_ptr() for f in frames], dtype=torch.int64).pin_memory().to(
+                    self.engine.device, non_blocking=True)
+            self._dev_frames, self._ptrs = frames, ptrs        # keep alive until the step has run
+            self.engine.track_enqueue(ptrs, self.use_graph)
         self.frame_id += 1
 
     def track(self, images):

@@ -50,7 +50,7 @@ def test_teacher_forced_single_sequence(ptype, modality, seed):
         assert ok or bool(near_tie.is_near_tie(ref.last["out"], ref.window)[0]), \
             "frame %d: box %.3f px, score map %.2e, and the reference is not at a near-tie" % (t, d, sm_err)
         # teacher forcing: overwrite the device state with the oracle's box
-        trk._impl.engine.buffer("state").copy_(torch.tensor([r["target_bbox"]], dtype=torch.float64))
+        trk._impl.set_state([r["target_bbox"]])
     assert good >= (T - 1) // 2, "only %d of %d frames agree" % (good, T - 1)
 
 
@@ -92,3 +92,28 @@ def test_too_small_box_raises():
     frames, _, _ = synth.synthetic_sequence(1, 1, "rgbe")
     with pytest.raises(Exception, match="Too small bounding box"):
         trk.initialize([frames[0]], [[5.0, 5.0, 0.0, 3.0]])
+
+
+def test_host_roi_upload_matches_device_frames():
+    """track(host frames) uploads only the search rectangle (csrc/engine3.cu); the boxes must be bit-identical
+    to the path that keeps whole frames on the device, including crops that overhang the frame."""
+    B, T = 3, 6
+    sd = synth.synthetic_state_dict("vipt_deep", 0)
+    seqs = [synth.synthetic_sequence(40 + i, T, "rgbt") for i in range(B)]
+    H, W = seqs[0][0][0].shape[:2]
+    boxes0 = [list(seqs[0][1]), [2.0, 3.0, 50.0, 40.0], [W - 45.0, H - 38.0, 60.0, 50.0]]   # interior, two corners
+    a = BatchedViPTTracker(sd, B, "vipt_deep", use_graph=False)
+    b = BatchedViPTTracker(sd, B, "vipt_deep", use_graph=False)
+    a.initialize([s[0][0] for s in seqs], boxes0)
+    b.initialize([torch.from_numpy(s[0][0]).cuda() for s in seqs], boxes0)
+    for t in range(1, T):
+        ba, sa = a.track([s[0][t] for s in seqs])
+        bb, sb = b.track([torch.from_numpy(s[0][t]).cuda() for s in seqs])
+        assert 0 < a.h2d_bytes < B * H * W * 6
+        np.testing.assert_array_equal(ba, bb)
+        np.testing.assert_array_equal(sa, sb)
+    # stale mirror (two steps enqueued without reading results) falls back to whole frames
+    a.track_async([s[0][1] for s in seqs]); a.track_async([s[0][2] for s in seqs])
+    assert a.h2d_bytes == B * H * W * 6
+    b.track_async([torch.from_numpy(s[0][1]).cuda() for s in seqs]); b.track_async([torch.from_numpy(s[0][2]).cuda() for s in seqs])
+    np.testing.assert_array_equal(a.engine.results()[0], b.engine.results()[0])
