@@ -6,6 +6,8 @@
 //
 // q, k, v are read straight out of the qkv GEMM output (B*N, 2304) with TMA (3-D map: column, token,
 // sequence), so tokens past N are zero-filled rather than belonging to the next sequence.
+#include <stdlib.h>
+
 #include "kernels.h"
 #include "sm100_ptx.cuh"
 
@@ -208,6 +210,15 @@ int attention_launch(const AttnOp& op, void* out, float* ce_prob, int ce_row, in
                              att_smem_bytes(kMaxKeys)) != cudaSuccess)
       return VIPT_ERR_LAUNCH;
     attr = true;
+  }
+  if (op.N > kQTile && !getenv("VIPT_ATTENTION_V1")) {
+    static int num_sms = 0;
+    if (!num_sms) {
+      int dev = 0;
+      cudaGetDevice(&dev);
+      cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    return attention2_launch(op, out, ce_prob, ce_row, lens_t, ce_stride, num_sms, st);
   }
   dim3 grid((op.N + kQTile - 1) / kQTile, 12, op.B);
   const float scale_log2 = 0.125f * 1.4426950408889634f;

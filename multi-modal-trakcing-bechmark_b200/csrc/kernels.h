@@ -36,7 +36,9 @@ struct AttnOp {
 };
 int attention_plan(AttnOp* op, const void* qkv, int B, int N);
 int attention_launch(const AttnOp& op, void* out, float* ce_prob, int ce_row, int lens_t, int ce_stride,
-                     cudaStream_t st);
+                     cudaStream_t st);     // N <= 128: one CTA per (sequence, head); else dispatches to attention2
+int attention2_launch(const AttnOp& op, void* out, float* ce_prob, int ce_row, int lens_t, int ce_stride, int num_sms,
+                      cudaStream_t st);    // persistent warp-specialised kernel (attention2.cu), N > 128
 
 int launch_im2col(const void* in, int c_total, int cin, int cin_stride, void* out, int B, int T, cudaStream_t st);
 int launch_head_final(const void* h4, const float* w5, const float* b5, const float* window, float* score_map,
