@@ -27,7 +27,7 @@ constexpr int kMaxKeys = 320;
 constexpr int kThreads = 448;
 constexpr int kOCol0 = 320, kOCol1 = 384;
 constexpr int kBoxBytes = 64 * 128;              // one TMA box: 64 tokens x 64 fp16
-enum { Q_FULL = 0, Q_EMPTY, K_FULL0, K_FULL1, K_EMPTY0, K_EMPTY1, V_FULL, V_EMPTY, S_FULL0, S_FULL1, P_FULL0, P_FULL1,
+enum { Q_FULL = 0, Q_EMPTY, K_FULL0, K_FULL1, K_EMPTY0, K_EMPTY1, V_FULL, V_EMPTY, S_FULL0, S_FULL1, S_EMPTY0, S_EMPTY1, P_FULL0, P_FULL1,
        O_FULL0, O_FULL1, O_EMPTY, ST_FULL0, ST_FULL1, NUM_BARS };
 __host__ __device__ constexpr int kboxes(int nkp) { return (nkp + 63) / 64; }
 __host__ __device__ constexpr int off_k(int) { return kQTile * 128; }
@@ -70,7 +70,7 @@ attention2_kernel(const __grid_constant__ CUtensorMap tm, op_t* __restrict__ out
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tm);
     for (int i = 0; i < NUM_BARS; ++i) {
-      const uint32_t cnt = (i == P_FULL0 || i == P_FULL1 || i == O_EMPTY) ? 4u : (i == ST_FULL0 || i == ST_FULL1) ? 8u : 1u;
+      const uint32_t cnt = (i == P_FULL0 || i == P_FULL1 || i == O_EMPTY || i == S_EMPTY0 || i == S_EMPTY1) ? 4u : (i == ST_FULL0 || i == ST_FULL1) ? 8u : 1u;
       mbar_init(&bars[i], cnt);
     }
     fence_mbar_init();
@@ -118,8 +118,8 @@ attention2_kernel(const __grid_constant__ CUtensorMap tm, op_t* __restrict__ out
       const uint32_t idesc_s0 = make_idesc(kQTile, w0), idesc_s1 = make_idesc(kQTile, w1);
       const uint32_t idesc_pv = make_idesc(kQTile, kHd, /*b_mn_major=*/true);
       const uint64_t qd = make_sdesc_sw128(smem_u32(sQ));
-      auto issue_pv = [&](int u, int c, bool first_of_item, bool last_of_item, int n_of_u) {
-        if (c == 0) {
+      auto issue_pv = [&](int u, int c, bool first_pv_of_tile, bool first_of_item, bool release_v, int n_of_u) {
+        if (first_pv_of_tile) {
           mbar_wait(&bars[O_EMPTY], (u & 1) ^ 1);          // epilogue of tile u-1 has drained O_0 / O_1
           if (first_of_item) mbar_wait(&bars[V_FULL], n_of_u & 1);
           tc_fence_after();
@@ -132,7 +132,7 @@ attention2_kernel(const __grid_constant__ CUtensorMap tm, op_t* __restrict__ out
           umma_f16(tmem + (c == 0 ? kOCol0 : kOCol1), pd, vd, idesc_pv, jj != 0);
         }
         umma_commit(&bars[O_FULL0 + c]);
-        if (c == 1 && last_of_item) umma_commit(&bars[V_EMPTY]);
+        if (release_v) umma_commit(&bars[V_EMPTY]);      // last P V of the item: V may be overwritten
       };
       int g = 0, n = 0;
       bool prev_first = false, prev_last = false;
@@ -143,22 +143,33 @@ attention2_kernel(const __grid_constant__ CUtensorMap tm, op_t* __restrict__ out
         for (int t = 0; t < T; ++t, ++g) {
           mbar_wait(&bars[Q_FULL], g & 1);
           tc_fence_after();
+          // Four events per tile, served in whatever order they fire: S buffer c drained -> issue S(g, c);
+          // P(g-1, c) written -> issue P V of the previous tile.
+          bool need_s[2] = {true, true}, need_pv[2] = {g > 0, g > 0};
+          bool pv_started = false;
+          while (need_s[0] | need_s[1] | need_pv[0] | need_pv[1]) {
 #pragma unroll
-          for (int c = 0; c < 2; ++c) {
-            if (g > 0) {                          // P(g-1, c) written  =>  S buffer c has been drained
-              mbar_wait(&bars[P_FULL0 + c], (g - 1) & 1);
-              tc_fence_after();
-            }
-            const uint64_t kd = make_sdesc_sw128(smem_u32(sK + kb * kbytes + (c == 0 ? 0 : c0) * 128));
+            for (int c = 0; c < 2; ++c) {
+              if (need_s[c] && (g == 0 || mbar_try_wait(&bars[S_EMPTY0 + c], (g - 1) & 1))) {
+                tc_fence_after();
+                const uint64_t kd = make_sdesc_sw128(smem_u32(sK + kb * kbytes + (c == 0 ? 0 : c0) * 128));
 #pragma unroll
-            for (int k = 0; k < kHd / 16; ++k)
-              umma_f16(tmem + (c == 0 ? 0 : c0), qd + 2 * k, kd + 2 * k, c == 0 ? idesc_s0 : idesc_s1, k != 0);
-            umma_commit(&bars[S_FULL0 + c]);
-            if (c == 1) {
-              umma_commit(&bars[Q_EMPTY]);
-              if (t == T - 1) umma_commit(&bars[K_EMPTY0 + kb]);
+                for (int k = 0; k < kHd / 16; ++k)
+                  umma_f16(tmem + (c == 0 ? 0 : c0), qd + 2 * k, kd + 2 * k, c == 0 ? idesc_s0 : idesc_s1, k != 0);
+                umma_commit(&bars[S_FULL0 + c]);
+                need_s[c] = false;
+                if (!need_s[c ^ 1]) {
+                  umma_commit(&bars[Q_EMPTY]);
+                  if (t == T - 1) umma_commit(&bars[K_EMPTY0 + kb]);
+                }
+              }
+              if (need_pv[c] && mbar_try_wait(&bars[P_FULL0 + c], (g - 1) & 1)) {
+                tc_fence_after();
+                issue_pv(g - 1, c, !pv_started, prev_first, prev_last && !need_pv[c ^ 1], prev_n);
+                pv_started = true;
+                need_pv[c] = false;
+              }
             }
-            if (g > 0) issue_pv(g - 1, c, prev_first, prev_last, prev_n);
           }
           prev_first = t == 0; prev_last = t == T - 1; prev_n = n;
         }
@@ -167,7 +178,7 @@ attention2_kernel(const __grid_constant__ CUtensorMap tm, op_t* __restrict__ out
         for (int c = 0; c < 2; ++c) {
           mbar_wait(&bars[P_FULL0 + c], (g - 1) & 1);
           tc_fence_after();
-          issue_pv(g - 1, c, prev_first, prev_last, prev_n);
+          issue_pv(g - 1, c, c == 0, prev_first, false, prev_n);
         }
       }
     }
@@ -186,30 +197,41 @@ attention2_kernel(const __grid_constant__ CUtensorMap tm, op_t* __restrict__ out
         mbar_wait(&bars[S_FULL0 + c], g & 1);
         tc_fence_after();
         if (q0 + wr * 32 < N) {                  // warp-uniform: at least one valid query row
-          float m = -INFINITY;
-          for (int gi = 0; gi < ngroups; ++gi) {
-            const int col = key0 + gi * 32;
-            uint32_t v[32];
-            tmem_ld32(t_row + col, v);
-            tmem_ld_wait();
+          // TMEM loads are software-pipelined: the load of group i+1 is in flight while group i is processed
+          float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};     // 4 independent chains (ILP)
+          auto max_group = [&](const uint32_t (&v)[32], int col) {
             if (col + 32 <= N) {
 #pragma unroll
-              for (int j = 0; j < 32; ++j) m = fmaxf(m, __uint_as_float(v[j]));
+              for (int j = 0; j < 32; j += 8) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                  m4[i] = fmaxf(m4[i], fmaxf(__uint_as_float(v[j + 2 * i]), __uint_as_float(v[j + 2 * i + 1])));
+              }
             } else {
 #pragma unroll
               for (int j = 0; j < 32; ++j)
-                if (col + j < N) m = fmaxf(m, __uint_as_float(v[j]));
+                if (col + j < N) m4[j & 3] = fmaxf(m4[j & 3], __uint_as_float(v[j]));
+            }
+          };
+          uint32_t va[32], vb[32];
+          tmem_ld32(t_row + key0, va);
+          for (int gi = 0; gi < ngroups; gi += 2) {
+            tmem_ld_wait();
+            if (gi + 1 < ngroups) tmem_ld32(t_row + key0 + (gi + 1) * 32, vb);
+            max_group(va, key0 + gi * 32);
+            if (gi + 1 < ngroups) {
+              tmem_ld_wait();
+              if (gi + 2 < ngroups) tmem_ld32(t_row + key0 + (gi + 2) * 32, va);
+              max_group(vb, key0 + (gi + 1) * 32);
             }
           }
+          tmem_ld32(t_row + key0, va);            // first group of pass 2, in flight during the wait below
+          const float m = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
           if (g > 0) mbar_wait(&bars[O_FULL0 + c], (g - 1) & 1);    // P V of the previous tile has consumed P_c
           const float msl = m * scale_log2;
           const bool ce_thread = ce_prob != nullptr && t == 0 && row == ce_row;
-          float sum = 0.f;
-          for (int gi = 0; gi < ngroups; ++gi) {
-            const int col = key0 + gi * 32;
-            uint32_t v[32];
-            tmem_ld32(t_row + col, v);
-            tmem_ld_wait();
+          float sum4[4] = {0.f, 0.f, 0.f, 0.f};
+          auto exp_group = [&](const uint32_t (&v)[32], int col) {
             float p[32];
 #pragma unroll
             for (int j = 0; j < 32; ++j) p[j] = ex2_approx(fmaf(__uint_as_float(v[j]), scale_log2, -msl));
@@ -219,7 +241,7 @@ attention2_kernel(const __grid_constant__ CUtensorMap tm, op_t* __restrict__ out
                 if (col + j >= N) p[j] = 0.f;
             }
 #pragma unroll
-            for (int j = 0; j < 32; ++j) sum += p[j];
+            for (int j = 0; j < 32; ++j) sum4[j & 3] += p[j];
             if (ce_thread) {
 #pragma unroll
               for (int j = 0; j < 32; ++j) s_ce[(n & 1) * kMaxKeys + col + j] = p[j];
@@ -235,10 +257,29 @@ attention2_kernel(const __grid_constant__ CUtensorMap tm, op_t* __restrict__ out
               const int chunk = (((col >> 5) & 1) * 4 + q) ^ (row & 7);
               *reinterpret_cast<uint4*>(prow + chunk * 16) = u;
             }
+          };
+          auto s_drained = [&]() {               // S_c is in registers: the MMA warp may overwrite it
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&bars[S_EMPTY0 + c]);
+          };
+          for (int gi = 0; gi < ngroups; gi += 2) {
+            tmem_ld_wait();
+            if (gi + 1 < ngroups) tmem_ld32(t_row + key0 + (gi + 1) * 32, vb); else s_drained();
+            exp_group(va, key0 + gi * 32);
+            if (gi + 1 < ngroups) {
+              tmem_ld_wait();
+              if (gi + 2 < ngroups) tmem_ld32(t_row + key0 + (gi + 2) * 32, va); else s_drained();
+              exp_group(vb, key0 + (gi + 1) * 32);
+            }
           }
           float* st = s_stats + (((g & 1) * 2 + c) * kQTile + row) * 2;
           st[0] = m;
-          st[1] = sum;
+          st[1] = (sum4[0] + sum4[1]) + (sum4[2] + sum4[3]);
+        }
+        else {
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&bars[S_EMPTY0 + c]);
         }
         fence_proxy_async_smem();
         tc_fence_before();

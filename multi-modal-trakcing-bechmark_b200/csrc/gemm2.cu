@@ -27,7 +27,8 @@ constexpr int kSlabBytes = BM * kSlabCols * 2;
 constexpr int kABytes = BM * BK * 2;
 constexpr int kBBytes = (BN / 2) * BK * 2;
 constexpr int kStageBytes = kABytes + kBBytes;
-constexpr int kThreads = 256;
+constexpr int kThreads = 384;          // warp 0 TMA, 1 MMA, 2 TMEM alloc, 4..11 epilogue (2 per TMEM lane group)
+constexpr int kEpiThreads = 256;
 constexpr int kSmemBytes = 1024 + kStages * kStageBytes + 2 * kSlabBytes + BN * 4 + (2 * kStages + 4) * 8 + 16;
 }  // namespace g2
 
@@ -72,18 +73,42 @@ __device__ __forceinline__ void umma_commit_2cta(uint64_t* bar) {     // arrives
       : "memory");
 }
 
-__device__ __forceinline__ float gelu_erf2(float x) {      // see gemm.cu
-  const float z = fabsf(x) * 0.70710678118654752f;
-  float t;
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, z, 1.0f)));
-  float p = fmaf(1.061405429f, t, -1.453152027f);
-  p = fmaf(p, t, 1.421413741f);
-  p = fmaf(p, t, -0.284496736f);
-  p = fmaf(p, t, 0.254829592f);
-  float e;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-1.4426950408889634f * z * z));
-  const float erf_abs = fmaf(-p * t, e, 1.0f);
-  return 0.5f * x + 0.5f * fabsf(x) * erf_abs;
+// GELU(x) = 0.5 x (1 + erf(x / sqrt 2)) with erf(z) = z * P(z^2), |z| clamped to 3.2: a degree-8 polynomial
+// evaluated entirely on the FMA pipe (max |erf error| 9e-5, below the fp16 resolution of the output).
+// The MUFU-based form (rcp + ex2 per element) made the fc1 epilogue XU-bound: 875 TFLOP/s vs 1230 for qkv.
+__device__ __forceinline__ uint64_t pk2(float a, float b) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+  return r;
+}
+__device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {   // packed fp32x2 FMA (sm_100)
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ uint64_t mul2(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+// two elements at a time: x0 = lo, x1 = hi
+__device__ __forceinline__ void gelu_erf2x2(float& x0, float& x1) {
+  const float z0 = fminf(fmaxf(x0 * 0.70710678118654752f, -3.2f), 3.2f);
+  const float z1 = fminf(fmaxf(x1 * 0.70710678118654752f, -3.2f), 3.2f);
+  const uint64_t z = pk2(z0, z1);
+  const uint64_t u = mul2(z, z);
+  uint64_t p = pk2(3.263779069e-08f, 3.263779069e-08f);
+  p = fma2(p, u, pk2(-1.673741013e-06f, -1.673741013e-06f));
+  p = fma2(p, u, pk2(3.751051790e-05f, 3.751051790e-05f));
+  p = fma2(p, u, pk2(-4.884092984e-04f, -4.884092984e-04f));
+  p = fma2(p, u, pk2(4.166864145e-03f, 4.166864145e-03f));
+  p = fma2(p, u, pk2(-2.504087559e-02f, -2.504087559e-02f));
+  p = fma2(p, u, pk2(1.111956437e-01f, 1.111956437e-01f));
+  p = fma2(p, u, pk2(-3.755427091e-01f, -3.755427091e-01f));
+  p = fma2(p, u, pk2(1.128344418e+00f, 1.128344418e+00f));
+  const uint64_t hx = mul2(pk2(x0, x1), pk2(0.5f, 0.5f));
+  const uint64_t r = fma2(hx, mul2(p, z), hx);
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(x0), "=f"(x1) : "l"(r));
 }
 
 template <int EPI>
@@ -123,7 +148,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tfull_bar[a], 1);
-      mbar_init(&tempty_bar[a], 8);   // 4 epilogue warps x 2 CTAs (leader's copy is the one used)
+      mbar_init(&tempty_bar[a], 16);  // 8 epilogue warps x 2 CTAs (leader's copy is the one used)
     }
     fence_mbar_init();
   }
@@ -184,7 +209,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     }
   } else if (warp >= 4) {
     // ------------------------------------------------ epilogue (both CTAs, own 128 rows)
-    const int we = warp - 4;
+    const int we = (warp - 4) & 3;           // TMEM lane group (warp % 4)
+    const int hh = (warp - 4) >> 2;          // which 32-column half of every 64-column slab
     const int et = threadIdx.x - 128;
     int as = 0;
     uint32_t aph = 0;
@@ -192,52 +218,47 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
       const int tn = t % tiles_n;
       const int tm = t / tiles_n;
       const int n0 = tn * BN;
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      for (int i = et; i < BN; i += 128) bias_s[i] = p.bias ? p.bias[n0 + i] : 0.f;
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      for (int i = et; i < BN; i += kEpiThreads) bias_s[i] = p.bias ? p.bias[n0 + i] : 0.f;
+      asm volatile("bar.sync 1, 256;" ::: "memory");
       mbar_wait(&tfull_bar[as], aph);
       tc_fence_after();
       const int row0 = tm * 2 * BM + (int)rank * BM;           // first row of this CTA's 128 x 256 tile
       const int r = we * 32 + lane;                            // row within the tile == TMEM lane
 #pragma unroll 1
       for (int sl = 0; sl < BN / kSlabCols; ++sl) {
-        uint32_t v0[32], v1[32];
-        const uint32_t taddr = tmem_base + as * BN + sl * kSlabCols + ((uint32_t)(we * 32) << 16);
-        tmem_ld32(taddr, v0);
-        tmem_ld32(taddr + 32, v1);
+        uint32_t v[32];
+        const uint32_t taddr = tmem_base + as * BN + sl * kSlabCols + hh * 32 + ((uint32_t)(we * 32) << 16);
+        tmem_ld32(taddr, v);
         uint8_t* buf = slab + (sl & 1) * kSlabBytes;
         // the TMA store that last read this staging buffer (two slabs ago) must have drained it
         if (et == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        asm volatile("bar.sync 1, 256;" ::: "memory");
         tmem_ld_wait();
         uint8_t* prow = buf + r * 128;
+        float f[32];
 #pragma unroll
-        for (int hh = 0; hh < 2; ++hh) {
-          float f[32];
+        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) + bias_s[sl * kSlabCols + hh * 32 + j];
+        if (EPI == EPI_GELU_F16) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j)
-            f[j] = __uint_as_float(hh == 0 ? v0[j] : v1[j]) + bias_s[sl * kSlabCols + hh * 32 + j];
-          if (EPI == EPI_GELU_F16) {
+          for (int j = 0; j < 32; j += 2) gelu_erf2x2(f[j], f[j + 1]);
+        }
+        if (EPI == EPI_RELU_F16) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) f[j] = gelu_erf2(f[j]);
-          }
-          if (EPI == EPI_RELU_F16) {
+          for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+        }
 #pragma unroll
-            for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
-          }
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            uint4 u;
-            u.x = pack_op2(f[q * 8 + 0], f[q * 8 + 1]);
-            u.y = pack_op2(f[q * 8 + 2], f[q * 8 + 3]);
-            u.z = pack_op2(f[q * 8 + 4], f[q * 8 + 5]);
-            u.w = pack_op2(f[q * 8 + 6], f[q * 8 + 7]);
-            const int chunk = (hh * 4 + q) ^ (r & 7);          // 128-byte swizzle, matches tmC
-            *reinterpret_cast<uint4*>(prow + chunk * 16) = u;
-          }
+        for (int q = 0; q < 4; ++q) {
+          uint4 u;
+          u.x = pack_op2(f[q * 8 + 0], f[q * 8 + 1]);
+          u.y = pack_op2(f[q * 8 + 2], f[q * 8 + 3]);
+          u.z = pack_op2(f[q * 8 + 4], f[q * 8 + 5]);
+          u.w = pack_op2(f[q * 8 + 6], f[q * 8 + 7]);
+          const int chunk = (hh * 4 + q) ^ (r & 7);          // 128-byte swizzle, matches tmC
+          *reinterpret_cast<uint4*>(prow + chunk * 16) = u;
         }
         fence_proxy_async_smem();
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        asm volatile("bar.sync 1, 256;" ::: "memory");
         if (et == 0) {
           asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
                        ::"l"(reinterpret_cast<uint64_t>(&tmC)), "r"(smem_u32(buf)), "r"(n0 + sl * kSlabCols), "r"(row0),
