@@ -232,11 +232,51 @@ def run_ours(args):
         "kernel_ms_per_step": {k: round(v[0], 4) for k, v in prof.items()},
         "kernel_share": {k: round(v[0] / step_ms_prof, 4) for k, v in prof.items()},
     }
+    if world == 1:
+        out["latency_bs1"] = latency_bs1(sd, seqs[0], dev)
     if world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline(sample_frames=args.cpu_frames)
     print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
+
+
+def latency_bs1(sd, seq, dev, n=300):
+    """BASELINE.json metric, second half: p50 per-frame latency at batch 1 (single sequence, CUDA-graph replay).
+    device: CUDA events around each enqueued step, frame resident in HBM; api: wall clock of the public
+    ViPTTrack-style call with a HOST frame (rectangle upload + step + box read-back)."""
+    from vipt_b200.tracker import BatchedViPTTracker
+    frames, box0 = seq
+    trk = BatchedViPTTracker(sd, 1, PROMPT, use_graph=True)
+    eng = trk.engine
+    host = [torch.from_numpy(np.ascontiguousarray(frames[t])).pin_memory() for t in range(RING + 1)]
+    devf = [h.to(dev) for h in host]
+    ptrs = [torch.tensor([f.data_ptr()], dtype=torch.int64).to(dev) for f in devf]
+    trk.initialize([devf[0]], [box0])
+    for k in range(10):
+        eng.track_enqueue(ptrs[1 + k % RING], True)
+    eng.results()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n)]
+    with torch.cuda.stream(eng.stream):
+        for k, (a, b) in enumerate(evs):
+            a.record()
+            eng.track_enqueue(ptrs[1 + k % RING], True)
+            b.record()
+    eng.stream.synchronize()
+    dev_ms = sorted(a.elapsed_time(b) for a, b in evs)
+    trk.initialize([host[0]], [box0])
+    for k in range(10):
+        trk.track([host[1 + k % RING]])
+    api_ms = []
+    for k in range(n):
+        t0 = time.perf_counter()
+        trk.track([host[1 + k % RING]])
+        api_ms.append((time.perf_counter() - t0) * 1e3)
+    api_ms.sort()
+    return {"p50_ms_device": dev_ms[n // 2], "p90_ms_device": dev_ms[int(n * 0.9)], "p50_ms_api_host_frame": api_ms[n // 2],
+            "p90_ms_api_host_frame": api_ms[int(n * 0.9)], "replays": n,
+            "how": "batch 1, CUDA-graph replay of the whole step; device = CUDA events per step, frame in HBM; "
+                   "api = wall clock of track(host frame) incl. rectangle upload and box read-back"}
 
 
 # ------------------------------------------------------------------------------------------------

@@ -8,7 +8,7 @@
 //
 // Each token row (768 fp32 + 768 fp16) is read from HBM exactly once and stays in registers across the
 // Fovea softmax, whose normaliser spans all positions of a sequence: a thread-block CLUSTER of 8 CTAs
-// owns one sequence (<= 40 rows per CTA, <= 5 rows per warp) and exchanges the per-channel softmax
+// owns one sequence (<= 40 rows per CTA, 16 warps, <= 3 rows per warp) and exchanges the per-channel softmax
 // statistics of its rows through distributed shared memory.
 //
 // The prompt stream itself is never materialised.  P_prev = conv1x1_{i-1}(F_prev) has rank 8, so
@@ -25,13 +25,13 @@ namespace vipt {
 namespace pf {
 constexpr int D = 768;
 constexpr int kCluster = 8;
-constexpr int kThreads = 256;
+constexpr int kThreads = 512;          // 16 warps: enough warps per scheduler to hide the per-row dependency chains
 constexpr int kWarps = kThreads / 32;
 constexpr float kLnEps = 1e-6f;
 // fold layout (floats), see PromptFoldHost in engine.cu
 constexpr int kCA = 0, kA = 8, kA0 = 72, kCD = 80, kG = 88, kH = 152, kC0 = 160, kSmooth = 161, kFoldFloats = 168;
 constexpr int kSmemBytes = 2 * 8 * D * 4 + kFoldFloats * 4 + 2 * 8 * 2 * 4 /*stat*/ + 2 * 8 * 2 * 4 /*M, invS*/ + 128 * 4 /*partials*/ +
-                           kWarps * 5 * (8 + 8 + 1) * 4 /* x0, x1, pos */ + 64;
+                           kWarps * 3 * (8 + 8 + 1) * 4 /* x0, x1, pos */ + 64;
 }  // namespace pf
 
 __device__ __forceinline__ float pf_warp_sum(float v) {
@@ -67,8 +67,8 @@ prompt_fused_kernel(float* __restrict__ x, const op_t* __restrict__ delta, int n
   float* s_ms = s_stat + 32;                     // [2][8][2]: global max, 1 / global sum
   float* s_wst = s_ms + 32;                      // [4 warps][2][8][2] partial statistics
   float* s_x0 = s_wst + 128;                     // [kWarps * RPW][8]
-  float* s_x1 = s_x0 + kWarps * 5 * 8;           // [kWarps * RPW][8]
-  int* s_pos = reinterpret_cast<int*>(s_x1 + kWarps * 5 * 8);
+  float* s_x1 = s_x0 + kWarps * 3 * 8;           // [kWarps * RPW][8]
+  int* s_pos = reinterpret_cast<int*>(s_x1 + kWarps * 3 * 8);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t rank = pf_cluster_rank();
@@ -354,12 +354,10 @@ int launch_prompt_fused(float* x, const void* delta, int n_cur, const int* gi, f
   const int rows_per_cta = (n_cur + pf::kCluster - 1) / pf::kCluster;
   const int rpw = (rows_per_cta + pf::kWarps - 1) / pf::kWarps;
   switch (rpw) {
-    case 1: case 2: case 3:
+    case 1: case 2:
+      return launch_pf<2>(x, delta, n_cur, gi, F, wg_a, fold, w1t, b1, gamma1, beta1, xn, B, lens_t, lens_full, st);
+    case 3:
       return launch_pf<3>(x, delta, n_cur, gi, F, wg_a, fold, w1t, b1, gamma1, beta1, xn, B, lens_t, lens_full, st);
-    case 4:
-      return launch_pf<4>(x, delta, n_cur, gi, F, wg_a, fold, w1t, b1, gamma1, beta1, xn, B, lens_t, lens_full, st);
-    case 5:
-      return launch_pf<5>(x, delta, n_cur, gi, F, wg_a, fold, w1t, b1, gamma1, beta1, xn, B, lens_t, lens_full, st);
   }
   return VIPT_ERR_ARG;
 }
