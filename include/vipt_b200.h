@@ -80,7 +80,7 @@ int vipt_engine_track_host(void* engine, const void* const* host_frames, int use
 int vipt_engine_set_state(void* engine, const double* boxes_host, void* stream);
 /* one un-graphed step with a CUDA-event pair around every kernel launch; sums (ms) and launch counts per
  * kernel class: 0 linear GEMMs, 1 head conv GEMMs, 2 attention, 3 prompt blocks, 4 LayerNorm/CE/final,
- * 5 crop, 6 im2col, 7 head tail.  Used by bench.py for the roofline line. */
+ * 5 crop, 6 (unused: the head convolutions are implicit GEMMs), 7 head tail.  Used by bench.py for the roofline line. */
 int vipt_engine_profile_step(void* engine, const void* frame_ptrs_dev, float* ms_by_class_host, int* n_by_class_host,
                              void* stream);
 int64_t vipt_engine_info(void* engine, const char* what);

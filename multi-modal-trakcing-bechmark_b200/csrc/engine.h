@@ -56,7 +56,7 @@ struct Engine {
   int ce_keep[kDepth];       // 0 if not a CE layer, else number of kept search tokens
 
   // activations
-  __half *apatch, *xn, *dbuf, *qkv, *att, *hbuf, *feat16, *a_col, *h1, *h2, *h3, *h4;
+  __half *apatch, *xn, *dbuf, *qkv, *att, *hbuf, *feat16, *h1, *h2, *h3, *h4;
   float *E, *xA, *xB, *XD, *FV, *ce_prob, *ce_score, *feat32;
   int *giA, *giB, *perm, *removed, *slot_of_pos, *ident, *err;
   // outputs / state

@@ -61,7 +61,6 @@ int Engine::finalize_buffers() {
   AL(xn, __half, R * 768); AL(dbuf, __half, R * 768); AL(qkv, __half, R * 2304); AL(att, __half, R * 768); AL(hbuf, __half, R * 3072);
   AL(ce_prob, float, (size_t)B * kHeads * kLensX); AL(ce_score, float, 3 * RH);
   AL(feat16, __half, RH * 768); AL(feat32, float, R * 768);
-  AL(a_col, __half, RH * 6912);        // largest im2col: conv1 (also holds 3 x RH x 2304 etc.)
   AL(h1, __half, RH * 768); AL(h2, __half, RH * 384); AL(h3, __half, RH * 192); AL(h4, __half, RH * 96);
   AL(giA, int, RH); AL(giB, int, RH); AL(perm, int, RH); AL(removed, int, 3 * RH); AL(slot_of_pos, int, RH);
   AL(ident, int, RH); AL(err, int, 1);
@@ -94,13 +93,11 @@ int Engine::finalize_buffers() {
     RET(gemm2_plan(&g_fc2[i], hbuf, 3072, L[i].w_fc2, 3072, Mm, 768, 3072, EPI_BIAS_F16, dbuf, 768, L[i].b_fc2));
   }
   const int MH = B * kLensX;
-  RET(gemm2_plan(&g_c1, a_col, 6912, w_c1, 6912, MH, 768, 6912, EPI_RELU_F16, h1, 768, b_c1));
-  RET(gemm_plan(&g_c2, a_col, 2304, (int64_t)MH * 2304, w_c2, 2304, 128 * 2304, 3, MH, 128, 2304, 128, EPI_RELU_F16, h2,
-                384, 0, 128, b_c2, nullptr));
-  RET(gemm_plan(&g_c3, a_col, 1152, (int64_t)MH * 1152, w_c3, 1152, 64 * 1152, 3, MH, 64, 1152, 64, EPI_RELU_F16, h3, 192,
-                0, 64, b_c3, nullptr));
-  RET(gemm_plan(&g_c4, a_col, 576, (int64_t)MH * 576, w_c4, 576, 32 * 576, 3, MH, 32, 576, 32, EPI_RELU_F16, h4, 96, 0,
-                32, b_c4, nullptr));
+  // center head: implicit 3x3 convolutions (no im2col buffer); BN folded, ReLU fused, towers grouped
+  RET(gemm2_plan_conv(&g_c1, feat16, 768, 768, w_c1, B, 768, EPI_RELU_F16, h1, 768, b_c1));
+  RET(gemm_plan_conv(&g_c2, h1, 768, 256, 256, w_c2, 3, B, 128, 128, EPI_RELU_F16, h2, 384, 128, b_c2));
+  RET(gemm_plan_conv(&g_c3, h2, 384, 128, 128, w_c3, 3, B, 64, 64, EPI_RELU_F16, h3, 192, 64, b_c3));
+  RET(gemm_plan_conv(&g_c4, h3, 192, 64, 64, w_c4, 3, B, 32, 32, EPI_RELU_F16, h4, 96, 32, b_c4));
   finalized = true;
   return VIPT_OK;
 }
@@ -178,14 +175,10 @@ int Engine::run_backbone_head(bool tracking, bool want_feat32, int debug_stop, c
   LAUNCH(K_NORM, launch_final_norm(x, dbuf, n_tok[kDepth], slot_of_pos, norm_g, norm_b, feat16, want_feat32 ? feat32 : nullptr, B, kLensT,
                         kLensFull, st));
   STAGE_END();   // 87: feat16
-  LAUNCH(K_IM2COL, launch_im2col(feat16, 768, 768, 0, a_col, B, 1, st));
   LAUNCH(K_GEMM_HEAD, gemm_launch(g_c1, num_sms, st));
   STAGE_END();   // 88: h1
-  LAUNCH(K_IM2COL, launch_im2col(h1, 768, 256, 256, a_col, B, 3, st));
   LAUNCH(K_GEMM_HEAD, gemm_launch(g_c2, num_sms, st));
-  LAUNCH(K_IM2COL, launch_im2col(h2, 384, 128, 128, a_col, B, 3, st));
   LAUNCH(K_GEMM_HEAD, gemm_launch(g_c3, num_sms, st));
-  LAUNCH(K_IM2COL, launch_im2col(h3, 192, 64, 64, a_col, B, 3, st));
   LAUNCH(K_GEMM_HEAD, gemm_launch(g_c4, num_sms, st));
   STAGE_END();   // 89: h4
   LAUNCH(K_HEAD_FINAL, launch_head_final(h4, w5, b5, window, score_map, size_map, offset_map, pred_boxes, tracking ? state : nullptr,

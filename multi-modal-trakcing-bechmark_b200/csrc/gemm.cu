@@ -102,7 +102,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         uint8_t* a_dst = tiles + s * Cfg::kStageBytes;
         uint8_t* b_dst = a_dst + Cfg::kABytes;
         mbar_expect_tx(&full_bar[s], Cfg::kStageBytes);
-        tma_load_3d(a_dst, &tmA, &full_bar[s], kb * BK, tm * BM, g);
+        if (p.conv_cb_per_tap) {      // implicit 3x3 conv: 128 rows = 8 image rows x 16 columns of sequence tm / 2
+          const int tap = kb / p.conv_cb_per_tap, cb = kb % p.conv_cb_per_tap;
+          tma_load_4d(a_dst, &tmA, &full_bar[s], g * p.conv_cin_stride + cb * BK, tap % 3 - 1, (tm & 1) * 8 + tap / 3 - 1,
+                      tm >> 1);
+        } else {
+          tma_load_3d(a_dst, &tmA, &full_bar[s], kb * BK, tm * BM, g);
+        }
         tma_load_3d(b_dst, &tmB, &full_bar[s], kb * BK, tn * BN, g);
         if (++s == Cfg::kStages) { s = 0; ph ^= 1; }
       }
@@ -287,28 +293,55 @@ int gemm_launch(const GemmOp& op, int num_sms, cudaStream_t st) {
   return VIPT_ERR_ARG;
 }
 
+// weight map + parameters (everything but the A map)
+static int plan_common(GemmOp* op, const void* W, int64_t ldw, int64_t w_group_stride, int G, int M, int N, int K, int bn,
+                       int epi, void* out, int64_t ldc, int64_t out_group_stride, int64_t out_group_col, const float* bias,
+                       const float* resid) {
+  if (K % BK != 0 || N % bn != 0 || (bn != 256 && bn != 128 && bn != 64 && bn != 32) || M <= 0 || G <= 0)
+    return VIPT_ERR_ARG;
+  if ((ldw * 2) % 16 != 0 || (reinterpret_cast<uintptr_t>(W) & 15)) return VIPT_ERR_ARG;
+  uint64_t db[3] = {(uint64_t)K, (uint64_t)N, (uint64_t)G};
+  uint64_t sb[2] = {(uint64_t)ldw * 2, (uint64_t)(G > 1 ? w_group_stride : (int64_t)N * ldw) * 2};
+  uint32_t bb[3] = {BK, (uint32_t)bn, 1};
+  int r = make_tmap_f16(&op->tmB, W, 3, db, sb, bb);
+  if (r) return r;
+  op->p.M = M; op->p.N = N; op->p.K = K; op->p.G = G;
+  op->p.out = out; op->p.ldc = ldc; op->p.out_group_stride = out_group_stride; op->p.out_group_col = out_group_col;
+  op->p.bias = bias; op->p.resid = resid;
+  op->p.conv_cb_per_tap = 0; op->p.conv_cin_stride = 0;
+  op->bn = bn; op->epi = epi;
+  return VIPT_OK;
+}
+
 int gemm_plan(GemmOp* op, const void* A, int64_t lda, int64_t a_group_stride, const void* W, int64_t ldw,
               int64_t w_group_stride, int G, int M, int N, int K, int bn, int epi, void* out, int64_t ldc,
               int64_t out_group_stride, int64_t out_group_col, const float* bias, const float* resid) {
-  if (K % BK != 0 || N % bn != 0 || (bn != 256 && bn != 128 && bn != 64 && bn != 32) || M <= 0 || G <= 0)
-    return VIPT_ERR_ARG;
-  if ((lda * 2) % 16 != 0 || (ldw * 2) % 16 != 0 || (reinterpret_cast<uintptr_t>(A) & 15) ||
-      (reinterpret_cast<uintptr_t>(W) & 15))
-    return VIPT_ERR_ARG;
+  if (M <= 0 || G <= 0 || (lda * 2) % 16 != 0 || (reinterpret_cast<uintptr_t>(A) & 15)) return VIPT_ERR_ARG;
   uint64_t da[3] = {(uint64_t)K, (uint64_t)M, (uint64_t)G};
   uint64_t sa[2] = {(uint64_t)lda * 2, (uint64_t)(G > 1 ? a_group_stride : (int64_t)M * lda) * 2};
   uint32_t ba[3] = {BK, BM, 1};
   int r = make_tmap_f16(&op->tmA, A, 3, da, sa, ba);
   if (r) return r;
-  uint64_t db[3] = {(uint64_t)K, (uint64_t)N, (uint64_t)G};
-  uint64_t sb[2] = {(uint64_t)ldw * 2, (uint64_t)(G > 1 ? w_group_stride : (int64_t)N * ldw) * 2};
-  uint32_t bb[3] = {BK, (uint32_t)bn, 1};
-  r = make_tmap_f16(&op->tmB, W, 3, db, sb, bb);
+  return plan_common(op, W, ldw, w_group_stride, G, M, N, K, bn, epi, out, ldc, out_group_stride, out_group_col, bias, resid);
+}
+
+static int make_conv_tmap(CUtensorMap* tm, const void* feat, int c_total, int B) {
+  uint64_t d[4] = {(uint64_t)c_total, 16, 16, (uint64_t)B};
+  uint64_t sb[3] = {(uint64_t)c_total * 2, (uint64_t)16 * c_total * 2, (uint64_t)256 * c_total * 2};
+  uint32_t box[4] = {BK, 16, 8, 1};
+  return make_tmap_f16(tm, feat, 4, d, sb, box);
+}
+
+int gemm_plan_conv(GemmOp* op, const void* feat, int c_total, int cin, int cin_stride, const void* W, int G, int B, int N,
+                   int bn, int epi, void* out, int64_t ldc, int64_t out_group_col, const float* bias) {
+  if (cin % BK != 0 || (c_total * 2) % 16 != 0 || (reinterpret_cast<uintptr_t>(feat) & 15)) return VIPT_ERR_ARG;
+  const int K = 9 * cin, M = B * 256;
+  int r = make_conv_tmap(&op->tmA, feat, c_total, B);
   if (r) return r;
-  op->p.M = M; op->p.N = N; op->p.K = K; op->p.G = G;
-  op->p.out = out; op->p.ldc = ldc; op->p.out_group_stride = out_group_stride; op->p.out_group_col = out_group_col;
-  op->p.bias = bias; op->p.resid = resid;
-  op->bn = bn; op->epi = epi;
+  r = plan_common(op, W, K, (int64_t)N * K, G, M, N, K, bn, epi, out, ldc, 0, out_group_col, bias, nullptr);
+  if (r) return r;
+  op->p.conv_cb_per_tap = cin / BK;
+  op->p.conv_cin_stride = cin_stride;
   return VIPT_OK;
 }
 

@@ -24,6 +24,11 @@ struct GemmParams {
   int64_t out_group_col;     // column offset added per group g
   const float* bias;         // (G, N) or null
   const float* resid;        // same layout as out (fp32) or null
+  // implicit 3x3 convolution (pad 1) over a (B,16,16,C) fp16 feature map: A tiles are fetched by a 4-D TMA
+  // map with shifted (x, y) coordinates (out-of-bounds = zero padding); k-block kb = tap * cb_per_tap + cb,
+  // K order tap * cin + c; group g reads channels [g * conv_cin_stride, +cin).  0 = plain GEMM.
+  int conv_cb_per_tap;
+  int conv_cin_stride;
 };
 
 struct GemmOp {
@@ -37,6 +42,11 @@ int make_tmap_f16(CUtensorMap* out, const void* base, int rank, const uint64_t* 
 int gemm_plan(GemmOp* op, const void* A, int64_t lda, int64_t a_group_stride, const void* W, int64_t ldw,
               int64_t w_group_stride, int G, int M, int N, int K, int bn, int epi, void* out, int64_t ldc,
               int64_t out_group_stride, int64_t out_group_col, const float* bias, const float* resid);
+// conv variants: `feat` (B*256, c_total) fp16; A tensor map is built over (c_total, 16, 16, B)
+int gemm_plan_conv(GemmOp* op, const void* feat, int c_total, int cin, int cin_stride, const void* W, int G, int B, int N,
+                   int bn, int epi, void* out, int64_t ldc, int64_t out_group_col, const float* bias);
+int gemm2_plan_conv(GemmOp* op, const void* feat, int c_total, int cin, const void* W, int B, int N, int epi, void* out,
+                    int64_t ldc, const float* bias);
 int gemm_launch(const GemmOp& op, int num_sms, cudaStream_t st);   // dispatches 2-CTA plans (bn == 512) to gemm2
 // 2-CTA (cta_group::2) kernel for large single-group GEMMs with N % 256 == 0 (gemm2.cu)
 int gemm2_plan(GemmOp* op, const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, int epi,

@@ -58,6 +58,14 @@ __device__ __forceinline__ void tma_load_3d_2cta(void* smem_dst, const CUtensorM
       ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(bar_cluster_addr), "r"(c0), "r"(c1), "r"(c2)
       : "memory");
 }
+__device__ __forceinline__ void tma_load_4d_2cta(void* smem_dst, const CUtensorMap* m, uint32_t bar_cluster_addr, int c0,
+                                                 int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], "
+      "[%2];"
+      ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(bar_cluster_addr), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
 __device__ __forceinline__ void umma_f16_2cta(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
                                               uint32_t accumulate) {
   asm volatile(
@@ -177,7 +185,12 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         uint8_t* b_dst = a_dst + kABytes;
         if (leader) mbar_expect_tx(&full_bar[s], 2 * kStageBytes);
         const uint32_t bar = mapa_cta(smem_u32(&full_bar[s]), 0);
-        tma_load_3d_2cta(a_dst, &tmA, bar, kb * BK, tm * 2 * BM + (int)rank * BM, 0);
+        if (p.conv_cb_per_tap) {      // implicit 3x3 conv: the pair tile is one sequence's 16 x 16 map, 8 rows per CTA
+          const int tap = kb / p.conv_cb_per_tap, cb = kb % p.conv_cb_per_tap;
+          tma_load_4d_2cta(a_dst, &tmA, bar, cb * BK, tap % 3 - 1, (int)rank * 8 + tap / 3 - 1, tm);
+        } else {
+          tma_load_3d_2cta(a_dst, &tmA, bar, kb * BK, tm * 2 * BM + (int)rank * BM, 0);
+        }
         tma_load_3d_2cta(b_dst, &tmB, bar, kb * BK, tn * BN + (int)rank * (BN / 2), 0);
         if (++s == kStages) { s = 0; ph ^= 1; }
       }
@@ -335,8 +348,26 @@ int gemm2_plan(GemmOp* op, const void* A, int64_t lda, const void* W, int64_t ld
   op->p.M = M; op->p.N = N; op->p.K = K; op->p.G = 1;
   op->p.out = out; op->p.ldc = ldc; op->p.out_group_stride = 0; op->p.out_group_col = 0;
   op->p.bias = bias; op->p.resid = nullptr;
+  op->p.conv_cb_per_tap = 0; op->p.conv_cin_stride = 0;
   op->bn = 512;      // marks a 2-CTA plan
   op->epi = epi;
+  return VIPT_OK;
+}
+
+int gemm2_plan_conv(GemmOp* op, const void* feat, int c_total, int cin, const void* W, int B, int N, int epi, void* out,
+                    int64_t ldc, const float* bias) {
+  if (cin % g2::BK != 0 || (c_total * 2) % 16 != 0) return VIPT_ERR_ARG;
+  const int K = 9 * cin;
+  // the plain plan builds valid W / C maps; its A map (a (M, K) view that does not exist) is replaced below
+  int r = gemm2_plan(op, W, K, W, K, B * 256, N, K, epi, out, ldc, bias);
+  if (r) return r;
+  uint64_t d[4] = {(uint64_t)c_total, 16, 16, (uint64_t)B};
+  uint64_t sb[3] = {(uint64_t)c_total * 2, (uint64_t)16 * c_total * 2, (uint64_t)256 * c_total * 2};
+  uint32_t box[4] = {g2::BK, 16, 8, 1};
+  r = make_tmap_f16(&op->tmA, feat, 4, d, sb, box);
+  if (r) return r;
+  op->p.conv_cb_per_tap = cin / g2::BK;
+  op->p.conv_cin_stride = 0;
   return VIPT_OK;
 }
 

@@ -1,4 +1,4 @@
-// Center head around the conv GEMMs: im2col for the 3x3 convolutions (zero padding 1) and the fused
+// Center head around the conv GEMMs (implicit 3x3 convolutions: gemm.cu / gemm2.cu conv mode): the fused
 // tail (1x1 conv5 of the three towers, sigmoid/clamp, Hann window, argmax, box decode, map_box_back,
 // clip_box, state update).  Reference: ViPT/lib/models/layers/head.py:130-201,
 // ViPT/lib/test/tracker/vipt.py:78-88,112-118, ViPT/lib/utils/box_ops.py:97-106.
@@ -6,37 +6,6 @@
 #include "sm100_ptx.cuh"
 
 namespace vipt {
-
-// in : (B, 256, c_total) fp16, tower t reads channels [t*cin_stride, t*cin_stride + cin)
-// out: (T, B*256, 9*cin) fp16, column = tap*cin + c, tap = ky*3 + kx
-__global__ void __launch_bounds__(256)
-im2col3x3_kernel(const op_t* __restrict__ in, int c_total, int cin, int cin_stride, op_t* __restrict__ out, int B,
-                 int T) {
-  const int vec_per_row = 9 * cin / 8;
-  const size_t total = (size_t)T * B * 256 * vec_per_row;
-  for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < total; i += (size_t)gridDim.x * 256) {
-    const int vc = (int)(i % vec_per_row);
-    const size_t rowi = i / vec_per_row;
-    const int pos = (int)(rowi % 256);
-    const int b = (int)((rowi / 256) % B);
-    const int t = (int)(rowi / ((size_t)256 * B));
-    const int tap = (vc * 8) / cin, c = (vc * 8) % cin;
-    const int y = (pos >> 4) + tap / 3 - 1, x = (pos & 15) + tap % 3 - 1;
-    uint4 v = make_uint4(0, 0, 0, 0);
-    if (y >= 0 && y < 16 && x >= 0 && x < 16)
-      v = *reinterpret_cast<const uint4*>(in + ((size_t)b * 256 + y * 16 + x) * c_total + t * cin_stride + c);
-    *reinterpret_cast<uint4*>(out + i * 8) = v;
-  }
-}
-
-int launch_im2col(const void* in, int c_total, int cin, int cin_stride, void* out, int B, int T, cudaStream_t st) {
-  const size_t total = (size_t)T * B * 256 * (9 * cin / 8);
-  size_t grid = (total + 255) / 256;
-  if (grid > 148 * 16) grid = 148 * 16;
-  im2col3x3_kernel<<<(int)grid, 256, 0, st>>>(reinterpret_cast<const op_t*>(in), c_total, cin, cin_stride,
-                                             reinterpret_cast<op_t*>(out), B, T);
-  return cudaGetLastError() == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
-}
 
 __device__ __forceinline__ float sigmoid_clamp(float v) {
   const float s = 1.0f / (1.0f + expf(-v));

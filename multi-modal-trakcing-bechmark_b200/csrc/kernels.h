@@ -40,7 +40,6 @@ int attention_launch(const AttnOp& op, void* out, float* ce_prob, int ce_row, in
 int attention2_launch(const AttnOp& op, void* out, float* ce_prob, int ce_row, int lens_t, int ce_stride, int num_sms,
                       cudaStream_t st);    // persistent warp-specialised kernel (attention2.cu), N > 128
 
-int launch_im2col(const void* in, int c_total, int cin, int cin_stride, void* out, int B, int T, cudaStream_t st);
 int launch_head_final(const void* h4, const float* w5, const float* b5, const float* window, float* score_map,
                       float* size_map, float* offset_map, float* pred_boxes, double* state, const double* geom,
                       const int* frame_hw, double* out_boxes, float* out_scores, int B, cudaStream_t st);
