@@ -44,6 +44,16 @@ int vipt_op_crop(const void* frame_ptrs_dev, const int* hw_dev, const double* bo
  * (ViPT/lib/models/layers/attn.py:33-59, attn_blocks.py:44-53). */
 int vipt_op_attention(const void* qkv, int B, int N, void* out, float* ce_prob, void* stream);
 
+/* Frame assembly after image decode (get_x_frame / get_rgbd_frame, ViPT/lib/train/dataset/depth_utils.py:7-132).
+ * rgbx: dtype 'rgbrgb' -- two BGR uint8 (H,W,3) images -> RGB||RGB uint8 (H,W,6).
+ * rgbd: dtype 'rgbcolormap' -- BGR uint8 (H,W,3) + uint16 depth (H,W): optional clip at min(3*median, 10000),
+ * min-max normalisation to [0,255], JET colour map (BGR order, as cv2.applyColorMap returns it) -> (H,W,6).
+ * workspace_dev: VIPT_ASSEMBLE_WORKSPACE_BYTES of device memory. */
+#define VIPT_ASSEMBLE_WORKSPACE_BYTES ((65536 + 4) * 4)
+int vipt_op_assemble_rgbx(const void* bgr_dev, const void* xbgr_dev, int H, int W, void* out_dev, void* stream);
+int vipt_op_assemble_rgbd(const void* bgr_dev, const void* depth16_dev, int H, int W, int depth_clip, void* out_dev,
+                          void* workspace_dev, void* stream);
+
 /* ---- engine: the drop-in for ViPTTrack.initialize/track (ViPT/lib/test/tracker/vipt.py:41-110) and for
  * build_viptrack(...).forward(template, search, ce_template_mask) (ViPT/lib/models/vipt/ostrack_prompt.py:39-58),
  * batched over `batch` independent sequences ---- */

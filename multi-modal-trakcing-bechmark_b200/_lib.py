@@ -22,6 +22,8 @@ SIGNATURES = {
     "vipt_op_crop": (c_int, [c_void_p, c_void_p, c_void_p, c_double, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                              c_int, c_void_p]),
     "vipt_op_attention": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "vipt_op_assemble_rgbx": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),
+    "vipt_op_assemble_rgbd": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "vipt_engine_create": (c_int, [ctypes.POINTER(c_void_p)]),
     "vipt_engine_destroy": (c_int, [c_void_p]),
     "vipt_engine_set_tensor": (c_int, [c_void_p, ctypes.c_char_p, c_void_p, c_i64]),

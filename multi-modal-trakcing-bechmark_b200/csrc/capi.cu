@@ -47,6 +47,16 @@ int vipt_op_attention(const void* qkv, int B, int N, void* out, float* ce_prob, 
   return vipt::attention_launch(op, out, ce_prob, vipt::kCeToken, vipt::kLensT, vipt::kLensX, (cudaStream_t)stream);
 }
 
+int vipt_op_assemble_rgbx(const void* bgr_dev, const void* xbgr_dev, int H, int W, void* out_dev, void* stream) {
+  if (!bgr_dev || !xbgr_dev || !out_dev || H < 1 || W < 1) return VIPT_ERR_ARG;
+  return vipt::launch_assemble_rgbx(bgr_dev, xbgr_dev, H, W, out_dev, (cudaStream_t)stream);
+}
+int vipt_op_assemble_rgbd(const void* bgr_dev, const void* depth16_dev, int H, int W, int depth_clip, void* out_dev,
+                          void* workspace_dev, void* stream) {
+  if (!bgr_dev || !depth16_dev || !out_dev || !workspace_dev || H < 1 || W < 1) return VIPT_ERR_ARG;
+  return vipt::launch_assemble_rgbd(bgr_dev, depth16_dev, H, W, depth_clip, out_dev, workspace_dev, (cudaStream_t)stream);
+}
+
 // ---------------------------------------------------------------- engine
 int vipt_engine_create(void** out) {
   if (!out) return VIPT_ERR_ARG;

@@ -30,6 +30,10 @@ int launch_ce_topk(const float* ce_prob, int n_heads, int n_s, int n_keep, const
 int launch_final_norm(const float* x, const void* delta, int n_cur, const int* slot_of_pos, const float* gamma, const float* beta,
                       void* feat16, float* feat32, int B, int lens_t, int lens_full, cudaStream_t st);
 
+int launch_assemble_rgbx(const void* bgr, const void* xbgr, int H, int W, void* out, cudaStream_t st);
+int launch_assemble_rgbd(const void* bgr, const void* depth16, int H, int W, int depth_clip, void* out, void* workspace,
+                         cudaStream_t st);
+
 struct AttnOp {
   CUtensorMap tm;
   int B, N, nkp;

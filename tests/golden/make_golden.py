@@ -6,6 +6,7 @@ Needs /root/reference (see oracle/ref_harness.py); the GPU box never runs this. 
   tests/golden/crop_golden.npz    cv2-backed sample_target + PreprocessorMM outputs
   tests/golden/model_golden.npz   build_viptrack(...).forward on seeded inputs (deep + shaw)
   tests/golden/track_golden.npz   ViPTTrack.initialize/track over seeded synthetic sequences
+  tests/golden/frames_golden.npz  get_x_frame ('rgbrgb', 'rgbcolormap' with / without depth clip) on synthetic PNGs
 Weights are not stored: vipt_b200.synth.synthetic_state_dict(seed) regenerates them.
 """
 import os
@@ -92,8 +93,44 @@ def track_golden():
     np.savez_compressed(os.path.join(OUT, "track_golden.npz"), **out)
 
 
+def frames_golden():
+    """get_x_frame (ViPT/lib/train/dataset/depth_utils.py:70-132) on small synthetic image files."""
+    import tempfile
+    import cv2
+    # the unmodified file, loaded by path: the package __init__ pulls in dataset classes (pycocotools, lmdb ...)
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("ref_depth_utils", os.path.join(rh.REF_ROOT, "lib", "train", "dataset",
+                                                                                  "depth_utils.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    get_x_frame = mod.get_x_frame
+    rng = np.random.default_rng(5)
+    out = {}
+    with tempfile.TemporaryDirectory() as d:
+        for i, (H, W) in enumerate(((48, 64), (37, 53), (60, 41))):
+            bgr = rng.integers(0, 256, (H, W, 3), dtype=np.uint8)
+            xbgr = rng.integers(0, 256, (H, W, 3), dtype=np.uint8)
+            yy, xx = np.mgrid[0:H, 0:W]
+            depth = (900 + 40 * yy + 25 * xx + rng.integers(0, 300, (H, W))).astype(np.uint16)
+            depth[rng.random((H, W)) < 0.05] = 0                    # holes, as in real depth maps
+            depth[rng.random((H, W)) < 0.03] = 60000                # far outliers (exercise the clip)
+            if i == 2:
+                depth[:] = 1234                                     # constant image: max == min
+            cv2.imwrite(os.path.join(d, "c.png"), bgr); cv2.imwrite(os.path.join(d, "x.png"), xbgr)
+            cv2.imwrite(os.path.join(d, "d.png"), depth)
+            out["bgr%d" % i], out["xbgr%d" % i], out["depth%d" % i] = bgr, xbgr, depth
+            out["rgbrgb%d" % i] = get_x_frame(os.path.join(d, "c.png"), os.path.join(d, "x.png"), dtype="rgbrgb")
+            for clip in (False, True):
+                out["rgbcolormap%d_clip%d" % (i, int(clip))] = get_x_frame(
+                    os.path.join(d, "c.png"), os.path.join(d, "d.png"), dtype="rgbcolormap", depth_clip=clip)
+    np.savez_compressed(os.path.join(OUT, "frames_golden.npz"), **out)
+
+
 if __name__ == "__main__":
+    if "--frames-only" in sys.argv:
+        frames_golden()
+        sys.exit(0)
     torch.set_num_threads(8)
-    crop_golden(); model_golden(); track_golden()
+    crop_golden(); model_golden(); track_golden(); frames_golden()
     for f in ("crop_golden.npz", "model_golden.npz", "track_golden.npz"):
         print(f, os.path.getsize(os.path.join(OUT, f)))
