@@ -47,7 +47,9 @@ __device__ __forceinline__ uint32_t mapa_cta(uint32_t local_addr, uint32_t rank)
   return r;
 }
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+  // relaxed: the barrier only orders TMEM reads (completed by tcgen05.wait::ld + fence::before_thread_sync);
+  // a release at cluster scope costs a MEMBAR.ALL per arrive
+  asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 // TMA load into this CTA's smem, completion signalled on a barrier that may live in the peer CTA
 __device__ __forceinline__ void tma_load_3d_2cta(void* smem_dst, const CUtensorMap* m, uint32_t bar_cluster_addr, int c0,
@@ -231,27 +233,25 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
       const int tn = t % tiles_n;
       const int tm = t / tiles_n;
       const int n0 = tn * BN;
-      asm volatile("bar.sync 1, 256;" ::: "memory");
+      // (bias_s of the previous tile was last read before that tile's final slab barrier)
       for (int i = et; i < BN; i += kEpiThreads) bias_s[i] = p.bias ? p.bias[n0 + i] : 0.f;
       asm volatile("bar.sync 1, 256;" ::: "memory");
       mbar_wait(&tfull_bar[as], aph);
       tc_fence_after();
       const int row0 = tm * 2 * BM + (int)rank * BM;           // first row of this CTA's 128 x 256 tile
       const int r = we * 32 + lane;                            // row within the tile == TMEM lane
+      const uint32_t taddr0 = tmem_base + as * BN + hh * 32 + ((uint32_t)(we * 32) << 16);
+      uint32_t v[32];
+      tmem_ld32(taddr0, v);
 #pragma unroll 1
       for (int sl = 0; sl < BN / kSlabCols; ++sl) {
-        uint32_t v[32];
-        const uint32_t taddr = tmem_base + as * BN + sl * kSlabCols + hh * 32 + ((uint32_t)(we * 32) << 16);
-        tmem_ld32(taddr, v);
         uint8_t* buf = slab + (sl & 1) * kSlabBytes;
-        // the TMA store that last read this staging buffer (two slabs ago) must have drained it
-        if (et == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
-        asm volatile("bar.sync 1, 256;" ::: "memory");
-        tmem_ld_wait();
         uint8_t* prow = buf + r * 128;
         float f[32];
+        tmem_ld_wait();
 #pragma unroll
         for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) + bias_s[sl * kSlabCols + hh * 32 + j];
+        if (sl + 1 < BN / kSlabCols) tmem_ld32(taddr0 + (sl + 1) * kSlabCols, v);     // in flight during the math below
         if (EPI == EPI_GELU_F16) {
 #pragma unroll
           for (int j = 0; j < 32; j += 2) gelu_erf2x2(f[j], f[j + 1]);
@@ -271,6 +271,9 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
           *reinterpret_cast<uint4*>(prow + chunk * 16) = u;
         }
         fence_proxy_async_smem();
+        // one barrier per slab: before it, the issuing thread makes sure the PREVIOUS store has drained its
+        // staging buffer, which is the buffer the next slab writes
+        if (et == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
         asm volatile("bar.sync 1, 256;" ::: "memory");
         if (et == 0) {
           asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
