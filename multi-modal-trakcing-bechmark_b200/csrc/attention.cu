@@ -211,13 +211,15 @@ int attention_launch(const AttnOp& op, void* out, float* ce_prob, int ce_row, in
       return VIPT_ERR_LAUNCH;
     attr = true;
   }
-  if (op.N > kQTile && !getenv("VIPT_ATTENTION_V1")) {
-    static int num_sms = 0;
-    if (!num_sms) {
-      int dev = 0;
-      cudaGetDevice(&dev);
-      cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
-    }
+  static int num_sms = 0;
+  if (!num_sms) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
+  }
+  // the persistent kernel needs >= one (sequence, head) item per SM to pay off; below that (latency mode) one CTA per
+  // 128-query tile keeps more SMs busy
+  if (op.N > kQTile && op.B * 12 >= num_sms && !getenv("VIPT_ATTENTION_V1")) {
     return attention2_launch(op, out, ce_prob, ce_row, lens_t, ce_stride, num_sms, st);
   }
   dim3 grid((op.N + kQTile - 1) / kQTile, 12, op.B);

@@ -82,19 +82,31 @@ int Engine::finalize_buffers() {
   const int M0 = B * kLensFull;
   RET(gemm_plan(&g_pe, apatch, 768, (int64_t)M0 * 768, w_pe, 768, 768 * 768, 2, M0, 768, 768, 256, EPI_BIAS_F32, E, 768,
                 (int64_t)M0 * 768, 0, b_pe, nullptr));
+  // Large batches: 2-CTA 256 x 256 tiles.  Small batches (latency mode): the pair kernel would fill only a few
+  // SMs, so the single-CTA kernel with narrow N tiles spreads the weight stream over the whole chip.
+  auto plan_lin = [&](GemmOp* op, const void* A, int64_t lda, const void* W, int M, int N, int K, int epi, void* out,
+                      const float* bias) -> int {
+    const int pair_tiles = ((M + 255) / 256) * (N / 256);
+    if (pair_tiles >= num_sms / 2) return gemm2_plan(op, A, lda, W, K, M, N, K, epi, out, N, bias);
+    const int mt = (M + 127) / 128;
+    int bn = 128;
+    if (mt * (N / 128) < num_sms) bn = 64;
+    return gemm_plan(op, A, lda, 0, W, K, 0, 1, M, N, K, bn, epi, out, N, 0, 0, bias, nullptr);
+  };
   for (int i = 0; i < kDepth; ++i) {
     const int Ma = B * n_tok[i], Mm = B * n_mlp[i];
-    RET(gemm2_plan(&g_qkv[i], xn, 768, L[i].w_qkv, 768, Ma, 2304, 768, EPI_BIAS_F16, qkv, 2304, L[i].b_qkv));
+    RET(plan_lin(&g_qkv[i], xn, 768, L[i].w_qkv, Ma, 2304, 768, EPI_BIAS_F16, qkv, L[i].b_qkv));
     RET(attention_plan(&a_op[i], qkv, B, n_tok[i]));
     // proj / fc2 write their branch output as fp16 (dbuf); the residual add is fused into the next
     // LayerNorm / prompt kernel, where it is coalesced
-    RET(gemm2_plan(&g_proj[i], att, 768, L[i].w_proj, 768, Ma, 768, 768, EPI_BIAS_F16, dbuf, 768, L[i].b_proj));
-    RET(gemm2_plan(&g_fc1[i], xn, 768, L[i].w_fc1, 768, Mm, 3072, 768, EPI_GELU_F16, hbuf, 3072, L[i].b_fc1));
-    RET(gemm2_plan(&g_fc2[i], hbuf, 3072, L[i].w_fc2, 3072, Mm, 768, 3072, EPI_BIAS_F16, dbuf, 768, L[i].b_fc2));
+    RET(plan_lin(&g_proj[i], att, 768, L[i].w_proj, Ma, 768, 768, EPI_BIAS_F16, dbuf, L[i].b_proj));
+    RET(plan_lin(&g_fc1[i], xn, 768, L[i].w_fc1, Mm, 3072, 768, EPI_GELU_F16, hbuf, L[i].b_fc1));
+    RET(plan_lin(&g_fc2[i], hbuf, 3072, L[i].w_fc2, Mm, 768, 3072, EPI_BIAS_F16, dbuf, L[i].b_fc2));
   }
   const int MH = B * kLensX;
   // center head: implicit 3x3 convolutions (no im2col buffer); BN folded, ReLU fused, towers grouped
-  RET(gemm2_plan_conv(&g_c1, feat16, 768, 768, w_c1, B, 768, EPI_RELU_F16, h1, 768, b_c1));
+  if (B * 3 >= num_sms / 2) RET(gemm2_plan_conv(&g_c1, feat16, 768, 768, w_c1, B, 768, EPI_RELU_F16, h1, 768, b_c1));
+  else RET(gemm_plan_conv(&g_c1, feat16, 768, 768, 0, w_c1, 1, B, 768, 64, EPI_RELU_F16, h1, 768, 0, b_c1));
   RET(gemm_plan_conv(&g_c2, h1, 768, 256, 256, w_c2, 3, B, 128, 128, EPI_RELU_F16, h2, 384, 128, b_c2));
   RET(gemm_plan_conv(&g_c3, h2, 384, 128, 128, w_c3, 3, B, 64, 64, EPI_RELU_F16, h3, 192, 64, b_c3));
   RET(gemm_plan_conv(&g_c4, h3, 192, 64, 64, w_c4, 3, B, 32, 32, EPI_RELU_F16, h4, 96, 32, b_c4));

@@ -33,20 +33,12 @@ struct GemmCfg {
   static constexpr int kSmemBytes = 1024 + kStages * kStageBytes + BN * 4 + (2 * kStages + 4) * 8 + 16;
 };
 
-// Exact-erf GELU (nn.GELU default, vit_ce_prompt.py:122) with erf from Abramowitz-Stegun 7.1.26
-// (|abs err| <= 1.5e-7, far below the fp16 output rounding): branch-free, 2 MUFU + ~12 FMA-pipe ops.
+// GELU: the polynomial-erf form shared with the 2-CTA kernel (sm100_ptx.cuh), so that small and large batches
+// produce identical activations.
 __device__ __forceinline__ float gelu_erf(float x) {
-  const float z = fabsf(x) * 0.70710678118654752f;
-  float t;
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, z, 1.0f)));
-  float p = fmaf(1.061405429f, t, -1.453152027f);
-  p = fmaf(p, t, 1.421413741f);
-  p = fmaf(p, t, -0.284496736f);
-  p = fmaf(p, t, 0.254829592f);
-  float e;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-1.4426950408889634f * z * z));
-  const float erf_abs = fmaf(-p * t, e, 1.0f);          // erf(|x|/sqrt2)
-  return 0.5f * x + 0.5f * fabsf(x) * erf_abs;           // 0.5 x (1 + sign(x) erf(|x|/sqrt2))
+  float a = x, b = 0.f;
+  gelu_erf2x2(a, b);
+  return a;
 }
 
 template <int BN, int EPI>
@@ -171,7 +163,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) + bias_s[c * 32 + j];
         if (EPI == EPI_GELU_F16) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = gelu_erf(f[j]);
+          for (int j = 0; j < 32; j += 2) gelu_erf2x2(f[j], f[j + 1]);
         }
         if (EPI == EPI_RELU_F16) {
 #pragma unroll

@@ -83,44 +83,6 @@ __device__ __forceinline__ void umma_commit_2cta(uint64_t* bar) {     // arrives
       : "memory");
 }
 
-// GELU(x) = 0.5 x (1 + erf(x / sqrt 2)) with erf(z) = z * P(z^2), |z| clamped to 3.2: a degree-8 polynomial
-// evaluated entirely on the FMA pipe (max |erf error| 9e-5, below the fp16 resolution of the output).
-// The MUFU-based form (rcp + ex2 per element) made the fc1 epilogue XU-bound: 875 TFLOP/s vs 1230 for qkv.
-__device__ __forceinline__ uint64_t pk2(float a, float b) {
-  uint64_t r;
-  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
-  return r;
-}
-__device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {   // packed fp32x2 FMA (sm_100)
-  uint64_t d;
-  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
-  return d;
-}
-__device__ __forceinline__ uint64_t mul2(uint64_t a, uint64_t b) {
-  uint64_t d;
-  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
-  return d;
-}
-// two elements at a time: x0 = lo, x1 = hi
-__device__ __forceinline__ void gelu_erf2x2(float& x0, float& x1) {
-  const float z0 = fminf(fmaxf(x0 * 0.70710678118654752f, -3.2f), 3.2f);
-  const float z1 = fminf(fmaxf(x1 * 0.70710678118654752f, -3.2f), 3.2f);
-  const uint64_t z = pk2(z0, z1);
-  const uint64_t u = mul2(z, z);
-  uint64_t p = pk2(3.263779069e-08f, 3.263779069e-08f);
-  p = fma2(p, u, pk2(-1.673741013e-06f, -1.673741013e-06f));
-  p = fma2(p, u, pk2(3.751051790e-05f, 3.751051790e-05f));
-  p = fma2(p, u, pk2(-4.884092984e-04f, -4.884092984e-04f));
-  p = fma2(p, u, pk2(4.166864145e-03f, 4.166864145e-03f));
-  p = fma2(p, u, pk2(-2.504087559e-02f, -2.504087559e-02f));
-  p = fma2(p, u, pk2(1.111956437e-01f, 1.111956437e-01f));
-  p = fma2(p, u, pk2(-3.755427091e-01f, -3.755427091e-01f));
-  p = fma2(p, u, pk2(1.128344418e+00f, 1.128344418e+00f));
-  const uint64_t hx = mul2(pk2(x0, x1), pk2(0.5f, 0.5f));
-  const uint64_t r = fma2(hx, mul2(p, z), hx);
-  asm("mov.b64 {%0, %1}, %2;" : "=f"(x0), "=f"(x1) : "l"(r));
-}
-
 template <int EPI>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(g2::kThreads, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,

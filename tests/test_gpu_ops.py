@@ -70,7 +70,8 @@ def test_crop_too_small_box_sets_error():
     assert err.item() == -5          # VIPT_ERR_SMALL_BOX <-> Exception('Too small bounding box.')
 
 
-@pytest.mark.parametrize("B,N", [(2, 320), (3, 244), (2, 190), (5, 153), (1, 64)])
+@pytest.mark.parametrize("B,N", [(2, 320), (3, 244), (2, 190), (5, 153), (1, 64),
+                                 (13, 320), (14, 244), (13, 190), (15, 153)])   # B * 12 >= #SMs: persistent kernel
 def test_attention(B, N):
     L = _lib.lib()
     g = torch.Generator(device="cuda").manual_seed(N)
