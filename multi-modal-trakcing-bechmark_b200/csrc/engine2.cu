@@ -90,7 +90,7 @@ int Engine::finalize_buffers() {
     if (pair_tiles >= num_sms / 2) return gemm2_plan(op, A, lda, W, K, M, N, K, epi, out, N, bias);
     const int mt = (M + 127) / 128;
     int bn = 128;
-    if (mt * (N / 128) < num_sms) bn = 64;
+    while (bn > 32 && mt * (N / bn) < num_sms) bn >>= 1;
     return gemm_plan(op, A, lda, 0, W, K, 0, 1, M, N, K, bn, epi, out, N, 0, 0, bias, nullptr);
   };
   for (int i = 0; i < kDepth; ++i) {
