@@ -1,6 +1,7 @@
 // Engine part 2: buffers, plans, per-step orchestration.
 #include <math.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "engine.h"
 
@@ -119,6 +120,7 @@ int Engine::finalize_buffers() {
 int Engine::run_backbone_head(bool tracking, bool want_feat32, int debug_stop, cudaStream_t st) {
   long nl = 0;
   int stage = 0;
+  static const bool use_cluster_prompt = getenv("VIPT_PROMPT_CLUSTER") != nullptr;
 #define LAUNCH(cls, expr)   \
   do {                      \
     prof_begin(cls, st);    \
@@ -152,8 +154,13 @@ int Engine::run_backbone_head(bool tracking, bool want_feat32, int debug_stop, c
     const int n = n_tok[i];
     if (i >= 1) {
       if (deep) {
-        LAUNCH(K_PROMPT, launch_prompt_fused(x, dbuf, n, gi, FV, PW[i].wg_a, PW[i].fold, PW[i].w1t, PW[i].b1, L[i].ln1_g,
-                                             L[i].ln1_b, xn, B, kLensT, kLensFull, st));
+        // cooperative persistent kernel (prompt_coop.cu); the cluster kernel (prompt_fused.cu) stays selectable
+        if (use_cluster_prompt)
+          LAUNCH(K_PROMPT, launch_prompt_fused(x, dbuf, n, gi, FV, PW[i].wg_a, PW[i].fold, PW[i].w1t, PW[i].b1, L[i].ln1_g,
+                                               L[i].ln1_b, xn, B, kLensT, kLensFull, st));
+        else
+          LAUNCH(K_PROMPT, launch_prompt_coop(x, dbuf, n, gi, FV, XD, PW[i].wg_a, PW[i].fold, PW[i].w1t, PW[i].b1,
+                                              L[i].ln1_g, L[i].ln1_b, xn, B, kLensT, kLensFull, num_sms, st));
       } else {
         LAUNCH(K_NORM, launch_ln_rows(x, n, dbuf, nullptr, 0, x, xn, L[i].ln1_g, L[i].ln1_b, B, n, kLensT, st));
       }

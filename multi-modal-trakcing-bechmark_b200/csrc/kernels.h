@@ -25,6 +25,9 @@ int launch_prompt_b(const float* F, const float* w1, const float* b1, float* P, 
 int launch_prompt_fused(float* x, const void* delta, int n_cur, const int* gi, float* F, const float* wg_a,
                         const float* fold, const float* w1t, const float* b1, const float* gamma1, const float* beta1,
                         void* xn, int B, int lens_t, int lens_full, cudaStream_t st);
+int launch_prompt_coop(float* x, const void* delta, int n_cur, const int* gi, float* F, float* X0, const float* wg_a,
+                       const float* fold, const float* w1t, const float* b1, const float* gamma1, const float* beta1,
+                       void* xn, int B, int lens_t, int lens_full, int num_sms, cudaStream_t st);
 int launch_ce_topk(const float* ce_prob, int n_heads, int n_s, int n_keep, const int* gi_in, int* gi_out, int* perm,
                    int* removed, int* slot_of_pos, float* score_out, int lens_x, int B, cudaStream_t st);
 int launch_final_norm(const float* x, const void* delta, int n_cur, const int* slot_of_pos, const float* gamma, const float* beta,

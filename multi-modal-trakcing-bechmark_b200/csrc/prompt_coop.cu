@@ -1,0 +1,300 @@
+// Deep-prompt stage of layers 1..11 (ViPT/lib/models/vipt/vit_ce_prompt.py:268-310) as ONE cooperative,
+// persistent kernel with a single grid-wide barrier (same mathematics as prompt_fused.cu, see there):
+//
+//   phase 1  every warp streams token rows (two at a time): v = x + delta, LayerNorm statistics and the
+//            768 -> 8 down-projection x0 = conv0_0(prompt_norms[i-1](v)); x0 goes to a small global array
+//   grid.sync()
+//   phase 2  per CTA: Fovea softmax statistics of the (<= 3) sequences its rows belong to, from x0;
+//            every warp re-reads its rows (L2 hits: they were read a few microseconds earlier by the same
+//            SM's neighbours), forms F = softmax * x0 + x1 (x1 from the previous layer's F by the rank-8
+//            algebra), adds the 8 -> 768 up-projection, writes x and xn = blocks[i].norm1(x) in fp16.
+//
+// The cluster version keeps rows in registers across a cluster barrier, which costs it occupancy (one CTA
+// per SM) and serialises load / math / barrier / math / store inside every CTA.  Here nothing is held
+// across the barrier: 16+ warps per SM stream independently, DRAM reads happen once (phase 2 hits L2).
+#include <cooperative_groups.h>
+
+#include "kernels.h"
+#include "sm100_ptx.cuh"
+
+namespace cg = cooperative_groups;
+
+namespace vipt {
+
+namespace pc {
+constexpr int D = 768;
+constexpr int kThreads = 256;
+constexpr int kWarps = kThreads / 32;
+constexpr int kMaxSeq = 4;             // sequences a CTA's row range may touch
+constexpr float kLnEps = 1e-6f;
+constexpr int kCA = 0, kA = 8, kA0 = 72, kCD = 80, kG = 88, kH = 152, kC0 = 160, kSmooth = 161, kFoldFloats = 168;
+constexpr int kSmemBytes = 2 * 8 * D * 4 + kFoldFloats * 4 + kMaxSeq * 32 * 4 + 2 * kThreads * 2 * 4 + 64;
+}  // namespace pc
+
+__device__ __forceinline__ float pc_warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+__device__ __forceinline__ void pc_load_row(const float* __restrict__ x, const op_t* __restrict__ delta, size_t row, int lane,
+                                            float4 (&v)[6]) {
+  const float4* xr = reinterpret_cast<const float4*>(x + row * pc::D);
+  const uint2* dr = reinterpret_cast<const uint2*>(delta + row * pc::D);
+#pragma unroll
+  for (int j = 0; j < 6; ++j) {
+    v[j] = xr[lane + 32 * j];
+    const uint2 u = dr[lane + 32 * j];
+    const float2 d0 = __half22float2(*reinterpret_cast<const __half2*>(&u.x));
+    const float2 d1 = __half22float2(*reinterpret_cast<const __half2*>(&u.y));
+    v[j].x += d0.x; v[j].y += d0.y; v[j].z += d1.x; v[j].w += d1.y;
+  }
+}
+
+__global__ void __launch_bounds__(pc::kThreads, 2)
+prompt_coop_kernel(float* __restrict__ x, const op_t* __restrict__ delta, int B, int n_cur, const int* __restrict__ gi,
+                   float* __restrict__ F, float* __restrict__ X0, const float* __restrict__ wg_a,
+                   const float* __restrict__ fold, const float* __restrict__ w1t, const float* __restrict__ b1,
+                   const float* __restrict__ gamma1, const float* __restrict__ beta1, op_t* __restrict__ xn, int lens_t,
+                   int lens_full) {
+  using namespace pc;
+  extern __shared__ float4 pc_smem4[];
+  float4* s_wa = pc_smem4;                       // [8][192] float4: conv0_0.weight * gamma_a
+  float4* s_w1 = s_wa + 8 * 192;                 // [8][192] float4: conv1x1.weight, k-major
+  float* s_fold = reinterpret_cast<float*>(s_w1 + 8 * 192);
+  float* s_ms = s_fold + kFoldFloats;            // [kMaxSeq][2 domains][8][2]: max, 1 / sum
+  float* s_red = s_ms + kMaxSeq * 32;            // [2][kThreads][2] reduction scratch
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int lens_x = lens_full - lens_t;
+  const int total = B * n_cur;
+  int rpc = (total + (int)gridDim.x - 1) / (int)gridDim.x;
+  rpc = (rpc + 1) & ~1;                          // even: rows are processed in pairs
+  const int row_lo = min((int)blockIdx.x * rpc, total), row_hi = min(row_lo + rpc, total);
+
+  for (int i = tid; i < 8 * 192; i += kThreads) {
+    s_wa[i] = reinterpret_cast<const float4*>(wg_a)[i];
+    s_w1[i] = reinterpret_cast<const float4*>(w1t)[i];
+  }
+  if (tid < kFoldFloats) s_fold[tid] = fold[tid];
+  __syncthreads();
+  const float smooth = s_fold[kSmooth];
+
+  // ------------------------------------------------------------------ phase 1: x0 per row
+  for (int r0 = row_lo + 2 * warp; r0 < row_hi; r0 += 2 * kWarps) {
+    const bool two = r0 + 1 < row_hi;
+    float4 v[2][6];
+    pc_load_row(x, delta, (size_t)r0, lane, v[0]);
+    if (two) pc_load_row(x, delta, (size_t)r0 + 1, lane, v[1]);
+    else {
+#pragma unroll
+      for (int j = 0; j < 6; ++j) v[1][j] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    float mean[2], q[2] = {0.f, 0.f}, dot[2][8];
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      float s = 0.f;
+#pragma unroll
+      for (int j = 0; j < 6; ++j) s += v[i][j].x + v[i][j].y + v[i][j].z + v[i][j].w;
+      mean[i] = pc_warp_sum(s) * (1.0f / D);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) dot[i][k] = 0.f;
+    }
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+      float4 a[2];
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        a[i] = make_float4(v[i][j].x - mean[i], v[i][j].y - mean[i], v[i][j].z - mean[i], v[i][j].w - mean[i]);
+        q[i] += a[i].x * a[i].x + a[i].y * a[i].y + a[i].z * a[i].z + a[i].w * a[i].w;
+      }
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float4 w = s_wa[k * 192 + lane + 32 * j];
+#pragma unroll
+        for (int i = 0; i < 2; ++i) dot[i][k] += w.x * a[i].x + w.y * a[i].y + w.z * a[i].z + w.w * a[i].w;
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      const float rstd = rsqrtf(pc_warp_sum(q[i]) * (1.0f / D) + kLnEps);
+      // transposed butterfly: 8 sums over 32 lanes in 9 shuffles; lane l ends with sum #(l >> 2)
+      float a4[4], a2[2];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const bool hi = lane & 16;
+        a4[k] = (hi ? dot[i][k + 4] : dot[i][k]) + __shfl_xor_sync(0xffffffffu, hi ? dot[i][k] : dot[i][k + 4], 16);
+      }
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        const bool hi = lane & 8;
+        a2[k] = (hi ? a4[k + 2] : a4[k]) + __shfl_xor_sync(0xffffffffu, hi ? a4[k] : a4[k + 2], 8);
+      }
+      const bool hi4 = lane & 4;
+      float c = (hi4 ? a2[1] : a2[0]) + __shfl_xor_sync(0xffffffffu, hi4 ? a2[0] : a2[1], 4);
+      c += __shfl_xor_sync(0xffffffffu, c, 2);
+      c += __shfl_xor_sync(0xffffffffu, c, 1);
+      if ((lane & 3) == 0 && (i == 0 || two)) X0[(size_t)(r0 + i) * 8 + (lane >> 2)] = c * rstd + s_fold[kCA + (lane >> 2)];
+    }
+  }
+  __threadfence();
+  cg::this_grid().sync();
+
+  // ------------------------------------------------------------------ phase 2, sequence by sequence
+  if (row_lo >= row_hi) return;
+  const int b_lo = row_lo / n_cur, b_hi = (row_hi - 1) / n_cur;
+  for (int b = b_lo; b <= b_hi; ++b) {
+    // Fovea softmax statistics of sequence b (all its kept rows, wherever they were computed):
+    // thread = (channel k, part); two block reductions (max, then sum of exp)
+    {
+      const int k = tid & 7, part = tid >> 3;
+      const float* x0b = X0 + (size_t)b * n_cur * 8;
+      float m[2] = {-INFINITY, -INFINITY};
+      for (int r = part; r < n_cur; r += kThreads / 8) {
+        const float l = __ldcg(x0b + r * 8 + k) * smooth;
+        m[r < lens_t ? 0 : 1] = fmaxf(m[r < lens_t ? 0 : 1], l);
+      }
+      __syncthreads();                           // s_red / s_ms of the previous sequence are no longer read
+      s_red[tid * 2] = m[0]; s_red[tid * 2 + 1] = m[1];
+      __syncthreads();
+      if (tid < 16) {
+        const int dom = tid >> 3, kk = tid & 7;
+        float M = -INFINITY;
+        for (int p = 0; p < kThreads / 8; ++p) M = fmaxf(M, s_red[(p * 8 + kk) * 2 + dom]);
+        const int n_removed = dom == 1 ? lens_x - (n_cur - lens_t) : 0;
+        if (n_removed > 0) M = fmaxf(M, smooth * s_fold[kCA + kk]);
+        s_ms[(dom * 8 + kk) * 2] = M;
+      }
+      __syncthreads();
+      float sm[2] = {0.f, 0.f};
+      for (int r = part; r < n_cur; r += kThreads / 8) {
+        const int dom = r < lens_t ? 0 : 1;
+        sm[dom] += expf(__ldcg(x0b + r * 8 + k) * smooth - s_ms[(dom * 8 + k) * 2]);
+      }
+      s_red[2 * kThreads + tid * 2] = sm[0]; s_red[2 * kThreads + tid * 2 + 1] = sm[1];
+      __syncthreads();
+      if (tid < 16) {
+        const int dom = tid >> 3, kk = tid & 7;
+        float S = 0.f;
+        for (int p = 0; p < kThreads / 8; ++p) S += s_red[2 * kThreads + (p * 8 + kk) * 2 + dom];
+        const int n_removed = dom == 1 ? lens_x - (n_cur - lens_t) : 0;
+        if (n_removed > 0) S += (float)n_removed * expf(smooth * s_fold[kCA + kk] - s_ms[(dom * 8 + kk) * 2]);
+        s_ms[(dom * 8 + kk) * 2 + 1] = 1.0f / S;
+      }
+      __syncthreads();
+    }
+    const int lo = max(row_lo, b * n_cur), hi = min(row_hi, (b + 1) * n_cur);
+    for (int r0 = lo + 2 * warp; r0 < hi; r0 += 2 * kWarps) {
+      const bool two = r0 + 1 < hi;
+      float4 v[2][6];
+      pc_load_row(x, delta, (size_t)r0, lane, v[0]);
+      if (two) pc_load_row(x, delta, (size_t)r0 + 1, lane, v[1]);
+      else {
+#pragma unroll
+        for (int j = 0; j < 6; ++j) v[1][j] = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+      // Fovea output of the two rows: lanes 0..7 -> row 0, lanes 8..15 -> row 1 (channel = lane & 7)
+      float fk = 0.f;
+      {
+        const int i = lane >> 3, k = lane & 7;
+        if (lane < 16 && (i == 0 || two)) {
+          const int r = r0 + i - b * n_cur;
+          const int pos = r < lens_t ? r : lens_t + gi[b * lens_x + (r - lens_t)];
+          const int dom = r < lens_t ? 0 : 1;
+          const float4 f0 = *reinterpret_cast<const float4*>(F + ((size_t)b * lens_full + pos) * 8);
+          const float4 f1 = *reinterpret_cast<const float4*>(F + ((size_t)b * lens_full + pos) * 8 + 4);
+          const float f[8] = {f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, f1.z, f1.w};
+          float var = s_fold[kC0], a = s_fold[kA0 + k];
+#pragma unroll
+          for (int p = 0; p < 8; ++p) {
+            float g = 0.f;
+#pragma unroll
+            for (int qq = 0; qq < 8; ++qq) g += s_fold[kG + p * 8 + qq] * f[qq];
+            var += f[p] * (g + 2.0f * s_fold[kH + p]);
+            a += s_fold[kA + k * 8 + p] * f[p];
+          }
+          const float x1 = a * rsqrtf(fmaxf(var, 0.f) + kLnEps) + s_fold[kCD + k];
+          const float x0 = __ldcg(X0 + (size_t)(r0 + i) * 8 + k);
+          fk = expf(x0 * smooth - s_ms[(dom * 8 + k) * 2]) * s_ms[(dom * 8 + k) * 2 + 1] * x0 + x1;
+          __syncwarp(0x0000ffffu >> (two ? 0 : 8));
+          F[((size_t)b * lens_full + pos) * 8 + k] = fk;       // all 8 lanes of a row have read F[pos] before this
+        }
+      }
+      float f[2][8], s[2] = {0.f, 0.f};
+#pragma unroll
+      for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int k = 0; k < 8; ++k) f[i][k] = __shfl_sync(0xffffffffu, fk, i * 8 + k);
+#pragma unroll
+      for (int j = 0; j < 6; ++j) {
+        const float4 bias = *reinterpret_cast<const float4*>(b1 + (lane + 32 * j) * 4);
+        float4 p[2] = {bias, bias};
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const float4 w = s_w1[k * 192 + lane + 32 * j];
+#pragma unroll
+          for (int i = 0; i < 2; ++i) {
+            p[i].x += w.x * f[i][k]; p[i].y += w.y * f[i][k]; p[i].z += w.z * f[i][k]; p[i].w += w.w * f[i][k];
+          }
+        }
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          v[i][j].x += p[i].x; v[i][j].y += p[i].y; v[i][j].z += p[i].z; v[i][j].w += p[i].w;
+          s[i] += v[i][j].x + v[i][j].y + v[i][j].z + v[i][j].w;
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        if (i == 1 && !two) break;
+        const size_t row = (size_t)r0 + i;
+        float4* xo = reinterpret_cast<float4*>(x + row * D);
+#pragma unroll
+        for (int j = 0; j < 6; ++j) xo[lane + 32 * j] = v[i][j];
+        const float mean = pc_warp_sum(s[i]) * (1.0f / D);
+        float q = 0.f;
+#pragma unroll
+        for (int j = 0; j < 6; ++j) {
+          const float a0 = v[i][j].x - mean, a1 = v[i][j].y - mean, a2 = v[i][j].z - mean, a3 = v[i][j].w - mean;
+          q += a0 * a0 + a1 * a1 + a2 * a2 + a3 * a3;
+        }
+        const float rstd = rsqrtf(pc_warp_sum(q) * (1.0f / D) + kLnEps);
+        uint2* no = reinterpret_cast<uint2*>(xn + row * D);
+#pragma unroll
+        for (int j = 0; j < 6; ++j) {
+          const float4 g = *reinterpret_cast<const float4*>(gamma1 + (lane + 32 * j) * 4);
+          const float4 be = *reinterpret_cast<const float4*>(beta1 + (lane + 32 * j) * 4);
+          uint2 u;
+          u.x = pack_op2((v[i][j].x - mean) * rstd * g.x + be.x, (v[i][j].y - mean) * rstd * g.y + be.y);
+          u.y = pack_op2((v[i][j].z - mean) * rstd * g.z + be.z, (v[i][j].w - mean) * rstd * g.w + be.w);
+          no[lane + 32 * j] = u;
+        }
+      }
+    }
+  }
+}
+
+int launch_prompt_coop(float* x, const void* delta, int n_cur, const int* gi, float* F, float* X0, const float* wg_a,
+                       const float* fold, const float* w1t, const float* b1, const float* gamma1, const float* beta1,
+                       void* xn, int B, int lens_t, int lens_full, int num_sms, cudaStream_t st) {
+  static int ctas_per_sm = 0;
+  if (!ctas_per_sm) {
+    if (cudaFuncSetAttribute(prompt_coop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, pc::kSmemBytes) != cudaSuccess ||
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, prompt_coop_kernel, pc::kThreads, pc::kSmemBytes) !=
+            cudaSuccess || ctas_per_sm < 1)
+      return VIPT_ERR_LAUNCH;
+  }
+  if (!delta || n_cur < lens_t || n_cur > lens_full) return VIPT_ERR_ARG;
+  const int total = B * n_cur;
+  int grid = ctas_per_sm * num_sms;
+  const int want = (total + 2 * pc::kWarps - 1) / (2 * pc::kWarps);     // at least one row pair per warp
+  if (grid > want) grid = want;
+  const op_t* d = reinterpret_cast<const op_t*>(delta);
+  op_t* xno = reinterpret_cast<op_t*>(xn);
+  void* args[] = {&x, &d, &B, &n_cur, &gi, &F, &X0, &wg_a, &fold, &w1t, &b1, &gamma1, &beta1, &xno, &lens_t, &lens_full};
+  if (cudaLaunchCooperativeKernel((const void*)prompt_coop_kernel, dim3(grid), dim3(pc::kThreads), args, pc::kSmemBytes, st) !=
+      cudaSuccess)
+    return VIPT_ERR_LAUNCH;
+  return VIPT_OK;
+}
+
+}  // namespace vipt
