@@ -41,6 +41,12 @@ GF_HEAD = 3.313
 GF_ATTN = 2.283
 GF_PROMPT = 0.142
 GF_TOTAL = 45.798
+# algorithmic operand bytes of the GEMM launches (fp16 A read + fp16 C written once; weights once per launch, per step)
+_TOK = 3 * (320 + 244 + 190 + 153)                                   # tokens x layers of one frame after CE
+GEMM_ACT_BYTES_PER_FRAME = _TOK * 2 * (768 + 2304 + 768 + 768 + 768 + 3072 + 3072 + 768) \
+    + 2 * 320 * 2 * (768 + 768) + 2 * 256 * (768 + 2 * 3 * 256 + 2 * 3 * 128 + 2 * 3 * 64 + 3 * 32)
+GEMM_WEIGHT_BYTES_PER_STEP = 2 * (12 * (768 * 2304 + 768 * 768 + 2 * 768 * 3072) + 2 * 768 * 768
+                                  + 3 * 9 * (768 * 256 + 256 * 128 + 128 * 64 + 64 * 32))
 
 
 def measured_peaks():
@@ -203,6 +209,8 @@ def run_ours(args):
     achieved = gemm_flops / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else None
     peak = float(peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops")))
     step_ms_prof = sum(v[0] for v in prof.values())
+    n_gemm = prof["gemm_linear"][1] + prof["gemm_head"][1]
+    traffic, traffic_src = gemm_traffic(B, n_gemm)
     out = {
         "metric": "ViPT-deep tracking frames/sec (crop+backbone+head+box update)", "value": value, "unit": "frames/s",
         "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak",
@@ -220,7 +228,9 @@ def run_ours(args):
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                     "frac": (achieved / peak) if achieved else None, "traffic": None,
+                     "frac": (achieved / peak) if achieved else None, "traffic": traffic, "traffic_unit": "bytes per launch",
+                     "traffic_source": traffic_src,
+                     "algorithmic_bytes_per_launch": (GEMM_ACT_BYTES_PER_FRAME * B + GEMM_WEIGHT_BYTES_PER_STEP) / max(1, n_gemm),
                      "kernel": "vipt::gemm_kernel (tcgen05, all linear + head-conv GEMM launches of a step)",
                      "peak_source": "%s bf16_tflops_sustained (kernel timed inside a long step)" % peak_src,
                      "algorithmic_gflop_per_frame": GF_LINEAR + GF_HEAD,
@@ -239,6 +249,23 @@ def run_ours(args):
     print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
+
+
+def gemm_traffic(B, n_gemm):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the GEMM launches of one step, per launch, from the committed ncu
+    launch list (profiles/r1_gemm_traffic.json, written by scripts/launch_summary.py --json).  None when the batch of
+    this run differs from the profiled one."""
+    p = os.path.join(ROOT, "profiles", "r1_gemm_traffic.json")
+    try:
+        j = json.load(open(p))
+    except (OSError, ValueError):
+        return None, "no profiles/r1_gemm_traffic.json"
+    if j.get("batch") != B:
+        return None, "profiles/r1_gemm_traffic.json is for batch %s" % j.get("batch")
+    steps = j.get("steps", 1)
+    tot = sum(k["dram_read_bytes"] + k["dram_write_bytes"] for n, k in j["kernels"].items() if n.startswith("gemm"))
+    n = sum(k["launches"] for name, k in j["kernels"].items() if name.startswith("gemm"))
+    return tot / max(1, n), "ncu dram__bytes_read+write over %d GEMM launches of %d steps (%s)" % (n, steps, j.get("source"))
 
 
 def latency_bs1(sd, seq, dev, n=300):
