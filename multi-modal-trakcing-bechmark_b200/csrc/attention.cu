@@ -126,16 +126,12 @@ attention_kernel(const __grid_constant__ CUtensorMap tm, op_t* __restrict__ out,
       for (int j = 0; j < 32; ++j) s_ce[c * 32 + j] = p[j];
     }
     // P[row][c*32 .. +32) -> swizzled K-major tile: block (c/2), 16-byte chunks (c%2)*4 .. +4
-    uint8_t* prow = smem + kSP + (c >> 1) * (kQTile * 128) + row * 128;
+    const uint32_t prow = smem_u32(smem + kSP) + (c >> 1) * (kQTile * 128) + row * 128;
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
-      uint4 u;
-      u.x = pack_op2(p[q * 8 + 0], p[q * 8 + 1]);
-      u.y = pack_op2(p[q * 8 + 2], p[q * 8 + 3]);
-      u.z = pack_op2(p[q * 8 + 4], p[q * 8 + 5]);
-      u.w = pack_op2(p[q * 8 + 6], p[q * 8 + 7]);
       const int chunk = ((c & 1) * 4 + q) ^ (row & 7);
-      *reinterpret_cast<uint4*>(prow + chunk * 16) = u;
+      sts128(prow + chunk * 16, pack_op2(p[q * 8 + 0], p[q * 8 + 1]), pack_op2(p[q * 8 + 2], p[q * 8 + 3]),
+             pack_op2(p[q * 8 + 4], p[q * 8 + 5]), pack_op2(p[q * 8 + 6], p[q * 8 + 7]));
     }
   }
   s_sum[hf * kQTile + row] = sum;
@@ -220,7 +216,8 @@ int attention_launch(const AttnOp& op, void* out, float* ce_prob, int ce_row, in
   // the persistent kernel needs >= one (sequence, head) item per SM to pay off; below that (latency mode) one CTA per
   // 128-query tile keeps more SMs busy
   if (op.N > kQTile && op.B * 12 >= num_sms && !getenv("VIPT_ATTENTION_V1")) {
-    return attention2_launch(op, out, ce_prob, ce_row, lens_t, ce_stride, num_sms, st);
+    if (getenv("VIPT_ATTENTION_V2")) return attention2_launch(op, out, ce_prob, ce_row, lens_t, ce_stride, num_sms, st);
+    return attention3_launch(op, out, ce_prob, ce_row, lens_t, ce_stride, num_sms, st);
   }
   dim3 grid((op.N + kQTile - 1) / kQTile, 12, op.B);
   const float scale_log2 = 0.125f * 1.4426950408889634f;

@@ -160,7 +160,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         tmem_ld_wait();
         float f[32];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) + bias_s[c * 32 + j];
+        for (int j = 0; j < 32; j += 4) {
+          const float4 bq = lds128f(smem_u32(bias_s) + (c * 32 + j) * 4);
+          f[j] = __uint_as_float(v[j]) + bq.x; f[j + 1] = __uint_as_float(v[j + 1]) + bq.y;
+          f[j + 2] = __uint_as_float(v[j + 2]) + bq.z; f[j + 3] = __uint_as_float(v[j + 3]) + bq.w;
+        }
         if (EPI == EPI_GELU_F16) {
 #pragma unroll
           for (int j = 0; j < 32; j += 2) gelu_erf2x2(f[j], f[j + 1]);

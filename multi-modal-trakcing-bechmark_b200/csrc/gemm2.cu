@@ -189,6 +189,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     const int we = (warp - 4) & 3;           // TMEM lane group (warp % 4)
     const int hh = (warp - 4) >> 2;          // which 32-column half of every 64-column slab
     const int et = threadIdx.x - 128;
+    const uint32_t bias_u32 = smem_u32(bias_s);
     int as = 0;
     uint32_t aph = 0;
     for (int t = cluster_id; t < num_tiles; t += num_clusters) {
@@ -208,11 +209,16 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
 #pragma unroll 1
       for (int sl = 0; sl < BN / kSlabCols; ++sl) {
         uint8_t* buf = slab + (sl & 1) * kSlabBytes;
-        uint8_t* prow = buf + r * 128;
+        const uint32_t prow = smem_u32(buf) + r * 128;
+        const uint32_t brow = bias_u32 + (sl * kSlabCols + hh * 32) * 4;
         float f[32];
         tmem_ld_wait();
 #pragma unroll
-        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) + bias_s[sl * kSlabCols + hh * 32 + j];
+        for (int j = 0; j < 32; j += 4) {
+          const float4 bq = lds128f(brow + j * 4);
+          f[j] = __uint_as_float(v[j]) + bq.x; f[j + 1] = __uint_as_float(v[j + 1]) + bq.y;
+          f[j + 2] = __uint_as_float(v[j + 2]) + bq.z; f[j + 3] = __uint_as_float(v[j + 3]) + bq.w;
+        }
         if (sl + 1 < BN / kSlabCols) tmem_ld32(taddr0 + (sl + 1) * kSlabCols, v);     // in flight during the math below
         if (EPI == EPI_GELU_F16) {
 #pragma unroll
@@ -224,13 +230,9 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         }
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-          uint4 u;
-          u.x = pack_op2(f[q * 8 + 0], f[q * 8 + 1]);
-          u.y = pack_op2(f[q * 8 + 2], f[q * 8 + 3]);
-          u.z = pack_op2(f[q * 8 + 4], f[q * 8 + 5]);
-          u.w = pack_op2(f[q * 8 + 6], f[q * 8 + 7]);
           const int chunk = (hh * 4 + q) ^ (r & 7);          // 128-byte swizzle, matches tmC
-          *reinterpret_cast<uint4*>(prow + chunk * 16) = u;
+          sts128(prow + chunk * 16, pack_op2(f[q * 8 + 0], f[q * 8 + 1]), pack_op2(f[q * 8 + 2], f[q * 8 + 3]),
+                 pack_op2(f[q * 8 + 4], f[q * 8 + 5]), pack_op2(f[q * 8 + 6], f[q * 8 + 7]));
         }
         fence_proxy_async_smem();
         // one barrier per slab: before it, the issuing thread makes sure the PREVIOUS store has drained its

@@ -46,6 +46,8 @@ int attention_launch(const AttnOp& op, void* out, float* ce_prob, int ce_row, in
                      cudaStream_t st);     // N <= 128: one CTA per (sequence, head); else dispatches to attention2
 int attention2_launch(const AttnOp& op, void* out, float* ce_prob, int ce_row, int lens_t, int ce_stride, int num_sms,
                       cudaStream_t st);    // persistent warp-specialised kernel (attention2.cu), N > 128
+int attention3_launch(const AttnOp& op, void* out, float* ce_prob, int ce_row, int lens_t, int ce_stride, int num_sms,
+                      cudaStream_t st);    // same, score MMAs running ahead of the softmax (attention3.cu)
 
 int launch_head_final(const void* h4, const float* w5, const float* b5, const float* window, float* score_map,
                       float* size_map, float* offset_map, float* pred_boxes, double* state, const double* geom,
