@@ -11,7 +11,12 @@
 //
 // The cluster version keeps rows in registers across a cluster barrier, which costs it occupancy (one CTA
 // per SM) and serialises load / math / barrier / math / store inside every CTA.  Here nothing is held
-// across the barrier: 16+ warps per SM stream independently, DRAM reads happen once (phase 2 hits L2).
+// across the barrier: 16 warps per SM stream independently, DRAM reads happen once (phase 2 hits L2).
+//
+// Rows reach the SM through a per-warp shared-memory slot filled by bulk async copies (cp.async.bulk +
+// mbarrier): while a warp works on one row pair from registers, the copy of its next pair is already in
+// flight, so ~150 KB per SM are outstanding all the time without spending registers on a second buffer
+// (the register-only version spent 42 % of its time waiting for the loads of the pair it was about to use).
 #include <cooperative_groups.h>
 
 #include "kernels.h"
@@ -23,12 +28,14 @@ namespace vipt {
 
 namespace pc {
 constexpr int D = 768;
-constexpr int kThreads = 256;
+constexpr int kThreads = 512;
 constexpr int kWarps = kThreads / 32;
 constexpr int kMaxSeq = 4;             // sequences a CTA's row range may touch
 constexpr float kLnEps = 1e-6f;
 constexpr int kCA = 0, kA = 8, kA0 = 72, kCD = 80, kG = 88, kH = 152, kC0 = 160, kSmooth = 161, kFoldFloats = 168;
-constexpr int kSmemBytes = 2 * 8 * D * 4 + kFoldFloats * 4 + kMaxSeq * 32 * 4 + 2 * kThreads * 2 * 4 + 64;
+constexpr int kSlotBytes = 2 * D * 4 + 2 * D * 2;      // one row pair: two fp32 rows, then two fp16 branch rows
+constexpr int kSmemBytes = 2 * 8 * D * 4 + 3 * D * 4 + kFoldFloats * 4 + kMaxSeq * 32 * 4 + 2 * kThreads * 2 * 4 +
+                           kWarps * kSlotBytes + kWarps * 8 + 64;
 }  // namespace pc
 
 __device__ __forceinline__ float pc_warp_sum(float v) {
@@ -37,21 +44,33 @@ __device__ __forceinline__ float pc_warp_sum(float v) {
   return v;
 }
 
-__device__ __forceinline__ void pc_load_row(const float* __restrict__ x, const op_t* __restrict__ delta, size_t row, int lane,
-                                            float4 (&v)[6]) {
-  const float4* xr = reinterpret_cast<const float4*>(x + row * pc::D);
-  const uint2* dr = reinterpret_cast<const uint2*>(delta + row * pc::D);
+// lane 0: start the bulk copies of rows [r0, r0 + nrows) (x fp32 and the branch output fp16) into this warp's slot
+__device__ __forceinline__ void pc_prefetch(const float* __restrict__ x, const op_t* __restrict__ delta, size_t r0, int nrows,
+                                            uint32_t slot, uint64_t* bar) {
+  const uint32_t xb = nrows * pc::D * 4, db = nrows * pc::D * 2;
+  fence_proxy_async_smem();                      // earlier generic reads of the slot are ordered before the async writes
+  mbar_expect_tx(bar, xb + db);
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(slot), "l"(x + r0 * pc::D), "r"(xb), "r"(smem_u32(bar)) : "memory");
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(slot + 2 * pc::D * 4), "l"(delta + r0 * pc::D), "r"(db), "r"(smem_u32(bar)) : "memory");
+}
+
+// v = x + delta of row `i` (0/1) of the slot
+__device__ __forceinline__ void pc_read_row(uint32_t slot, int i, int lane, float4 (&v)[6]) {
+  const uint32_t xa = slot + i * pc::D * 4 + lane * 16, da = slot + 2 * pc::D * 4 + i * pc::D * 2 + lane * 8;
 #pragma unroll
   for (int j = 0; j < 6; ++j) {
-    v[j] = xr[lane + 32 * j];
-    const uint2 u = dr[lane + 32 * j];
-    const float2 d0 = __half22float2(*reinterpret_cast<const __half2*>(&u.x));
-    const float2 d1 = __half22float2(*reinterpret_cast<const __half2*>(&u.y));
+    v[j] = lds128f(xa + j * 512);
+    uint32_t u0, u1;
+    asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(u0), "=r"(u1) : "r"(da + j * 256) : "memory");
+    const float2 d0 = __half22float2(*reinterpret_cast<const __half2*>(&u0));
+    const float2 d1 = __half22float2(*reinterpret_cast<const __half2*>(&u1));
     v[j].x += d0.x; v[j].y += d0.y; v[j].z += d1.x; v[j].w += d1.y;
   }
 }
 
-__global__ void __launch_bounds__(pc::kThreads, 2)
+__global__ void __launch_bounds__(pc::kThreads, 1)
 prompt_coop_kernel(float* __restrict__ x, const op_t* __restrict__ delta, int B, int n_cur, const int* __restrict__ gi,
                    float* __restrict__ F, float* __restrict__ X0, const float* __restrict__ wg_a,
                    const float* __restrict__ fold, const float* __restrict__ w1t, const float* __restrict__ b1,
@@ -61,9 +80,14 @@ prompt_coop_kernel(float* __restrict__ x, const op_t* __restrict__ delta, int B,
   extern __shared__ float4 pc_smem4[];
   float4* s_wa = pc_smem4;                       // [8][192] float4: conv0_0.weight * gamma_a
   float4* s_w1 = s_wa + 8 * 192;                 // [8][192] float4: conv1x1.weight, k-major
-  float* s_fold = reinterpret_cast<float*>(s_w1 + 8 * 192);
+  float4* s_b1 = s_w1 + 8 * 192;                 // [192] conv1x1.bias, then norm1 gamma, beta
+  float4* s_g1 = s_b1 + 192;
+  float4* s_be1 = s_g1 + 192;
+  float* s_fold = reinterpret_cast<float*>(s_be1 + 192);
   float* s_ms = s_fold + kFoldFloats;            // [kMaxSeq][2 domains][8][2]: max, 1 / sum
   float* s_red = s_ms + kMaxSeq * 32;            // [2][kThreads][2] reduction scratch
+  uint8_t* s_slots = reinterpret_cast<uint8_t*>(s_red + 2 * kThreads * 2);      // [kWarps][kSlotBytes], 16-byte aligned
+  uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_slots + kWarps * kSlotBytes);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int lens_x = lens_full - lens_t;
@@ -72,9 +96,23 @@ prompt_coop_kernel(float* __restrict__ x, const op_t* __restrict__ delta, int B,
   rpc = (rpc + 1) & ~1;                          // even: rows are processed in pairs
   const int row_lo = min((int)blockIdx.x * rpc, total), row_hi = min(row_lo + rpc, total);
 
+  const uint32_t slot = smem_u32(s_slots + warp * kSlotBytes);
+  uint64_t* bar = s_bar + warp;
+  uint32_t uses = 0;                             // completed phases of this warp's barrier
+  if (lane == 0) mbar_init(bar, 1);
+  fence_mbar_init();
+  __syncwarp();
+  // first row pair of phase 1: in flight while the weights are staged
+  if (lane == 0 && row_lo + 2 * warp < row_hi)
+    pc_prefetch(x, delta, (size_t)(row_lo + 2 * warp), min(2, row_hi - (row_lo + 2 * warp)), slot, bar);
   for (int i = tid; i < 8 * 192; i += kThreads) {
     s_wa[i] = reinterpret_cast<const float4*>(wg_a)[i];
     s_w1[i] = reinterpret_cast<const float4*>(w1t)[i];
+  }
+  if (tid < 192) {
+    s_b1[tid] = reinterpret_cast<const float4*>(b1)[tid];
+    s_g1[tid] = reinterpret_cast<const float4*>(gamma1)[tid];
+    s_be1[tid] = reinterpret_cast<const float4*>(beta1)[tid];
   }
   if (tid < kFoldFloats) s_fold[tid] = fold[tid];
   __syncthreads();
@@ -84,12 +122,16 @@ prompt_coop_kernel(float* __restrict__ x, const op_t* __restrict__ delta, int B,
   for (int r0 = row_lo + 2 * warp; r0 < row_hi; r0 += 2 * kWarps) {
     const bool two = r0 + 1 < row_hi;
     float4 v[2][6];
-    pc_load_row(x, delta, (size_t)r0, lane, v[0]);
-    if (two) pc_load_row(x, delta, (size_t)r0 + 1, lane, v[1]);
+    mbar_wait(bar, uses & 1); ++uses;
+    pc_read_row(slot, 0, lane, v[0]);
+    if (two) pc_read_row(slot, 1, lane, v[1]);
     else {
 #pragma unroll
       for (int j = 0; j < 6; ++j) v[1][j] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
+    __syncwarp();
+    if (lane == 0 && r0 + 2 * kWarps < row_hi)   // next pair of this warp: in flight during the math below
+      pc_prefetch(x, delta, (size_t)(r0 + 2 * kWarps), min(2, row_hi - (r0 + 2 * kWarps)), slot, bar);
     float mean[2], q[2] = {0.f, 0.f}, dot[2][8];
 #pragma unroll
     for (int i = 0; i < 2; ++i) {
@@ -144,6 +186,9 @@ prompt_coop_kernel(float* __restrict__ x, const op_t* __restrict__ delta, int B,
   if (row_lo >= row_hi) return;
   const int b_lo = row_lo / n_cur, b_hi = (row_hi - 1) / n_cur;
   for (int b = b_lo; b <= b_hi; ++b) {
+    const int lo = max(row_lo, b * n_cur), hi = min(row_hi, (b + 1) * n_cur);
+    // first row pair of this warp in the segment: in flight during the statistics below
+    if (lane == 0 && lo + 2 * warp < hi) pc_prefetch(x, delta, (size_t)(lo + 2 * warp), min(2, hi - (lo + 2 * warp)), slot, bar);
     // Fovea softmax statistics of sequence b (all its kept rows, wherever they were computed):
     // thread = (channel k, part); two block reductions (max, then sum of exp)
     {
@@ -183,16 +228,19 @@ prompt_coop_kernel(float* __restrict__ x, const op_t* __restrict__ delta, int B,
       }
       __syncthreads();
     }
-    const int lo = max(row_lo, b * n_cur), hi = min(row_hi, (b + 1) * n_cur);
     for (int r0 = lo + 2 * warp; r0 < hi; r0 += 2 * kWarps) {
       const bool two = r0 + 1 < hi;
       float4 v[2][6];
-      pc_load_row(x, delta, (size_t)r0, lane, v[0]);
-      if (two) pc_load_row(x, delta, (size_t)r0 + 1, lane, v[1]);
+      mbar_wait(bar, uses & 1); ++uses;
+      pc_read_row(slot, 0, lane, v[0]);
+      if (two) pc_read_row(slot, 1, lane, v[1]);
       else {
 #pragma unroll
         for (int j = 0; j < 6; ++j) v[1][j] = make_float4(0.f, 0.f, 0.f, 0.f);
       }
+      __syncwarp();
+      if (lane == 0 && r0 + 2 * kWarps < hi)
+        pc_prefetch(x, delta, (size_t)(r0 + 2 * kWarps), min(2, hi - (r0 + 2 * kWarps)), slot, bar);
       // Fovea output of the two rows: lanes 0..7 -> row 0, lanes 8..15 -> row 1 (channel = lane & 7)
       float fk = 0.f;
       {
@@ -227,7 +275,7 @@ prompt_coop_kernel(float* __restrict__ x, const op_t* __restrict__ delta, int B,
         for (int k = 0; k < 8; ++k) f[i][k] = __shfl_sync(0xffffffffu, fk, i * 8 + k);
 #pragma unroll
       for (int j = 0; j < 6; ++j) {
-        const float4 bias = *reinterpret_cast<const float4*>(b1 + (lane + 32 * j) * 4);
+        const float4 bias = s_b1[lane + 32 * j];
         float4 p[2] = {bias, bias};
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
@@ -261,8 +309,8 @@ prompt_coop_kernel(float* __restrict__ x, const op_t* __restrict__ delta, int B,
         uint2* no = reinterpret_cast<uint2*>(xn + row * D);
 #pragma unroll
         for (int j = 0; j < 6; ++j) {
-          const float4 g = *reinterpret_cast<const float4*>(gamma1 + (lane + 32 * j) * 4);
-          const float4 be = *reinterpret_cast<const float4*>(beta1 + (lane + 32 * j) * 4);
+          const float4 g = s_g1[lane + 32 * j];
+          const float4 be = s_be1[lane + 32 * j];
           uint2 u;
           u.x = pack_op2((v[i][j].x - mean) * rstd * g.x + be.x, (v[i][j].y - mean) * rstd * g.y + be.y);
           u.y = pack_op2((v[i][j].z - mean) * rstd * g.z + be.z, (v[i][j].w - mean) * rstd * g.w + be.w);
