@@ -105,8 +105,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         if (++s == Cfg::kStages) { s = 0; ph ^= 1; }
       }
     }
-  } else if (threadIdx.x == 32) {
-    // ------------------------------------------------ MMA issuer
+  } else if (warp == 1) {
+    // ------------------------------------------------ MMA issuer: warp-uniform loop, one elected lane issues
     constexpr uint32_t idesc = make_idesc(BM, BN);
     int s = 0;
     uint32_t ph = 0;
@@ -122,15 +122,19 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         const uint32_t a_addr = smem_u32(tiles + s * Cfg::kStageBytes);
         const uint64_t adesc = make_sdesc_sw128(a_addr);
         const uint64_t bdesc = make_sdesc_sw128(a_addr + Cfg::kABytes);
+        if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < BK / 16; ++k) {
-          // +32 B per K=16 step inside the 128B swizzle atom (start-address field is in 16 B units)
-          umma_f16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+          for (int k = 0; k < BK / 16; ++k) {
+            // +32 B per K=16 step inside the 128B swizzle atom (start-address field is in 16 B units)
+            umma_f16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+          }
+          umma_commit(&empty_bar[s]);
         }
-        umma_commit(&empty_bar[s]);
+        __syncwarp();
         if (++s == Cfg::kStages) { s = 0; ph ^= 1; }
       }
-      umma_commit(&tfull_bar[as]);
+      if (elect_one()) umma_commit(&tfull_bar[as]);
+      __syncwarp();
       if (++as == 2) { as = 0; aph ^= 1; }
     }
   } else if (warp >= 4) {

@@ -159,8 +159,10 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         if (++s == kStages) { s = 0; ph ^= 1; }
       }
     }
-  } else if (threadIdx.x == 32 && leader) {
-    // ------------------------------------------------ MMA issuer (leader CTA only)
+  } else if (warp == 1 && leader) {
+    // ------------------------------------------------ MMA issuer (leader CTA only).  The whole warp runs the loop so
+    // that barriers, stage indices and descriptors stay warp-uniform (uniform registers feed UTCHMMA directly; a
+    // single divergent thread made the compiler wrap every MMA in an R2UR broadcast loop); one elected lane issues.
     constexpr uint32_t idesc = make_idesc(2 * BM, BN);
     int s = 0;
     uint32_t ph = 0;
@@ -176,12 +178,16 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         const uint32_t a_addr = smem_u32(tiles + s * kStageBytes);
         const uint64_t adesc = make_sdesc_sw128(a_addr);
         const uint64_t bdesc = make_sdesc_sw128(a_addr + kABytes);
+        if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < BK / 16; ++k) umma_f16_2cta(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
-        umma_commit_2cta(&empty_bar[s]);
+          for (int k = 0; k < BK / 16; ++k) umma_f16_2cta(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+          umma_commit_2cta(&empty_bar[s]);
+        }
+        __syncwarp();
         if (++s == kStages) { s = 0; ph ^= 1; }
       }
-      umma_commit_2cta(&tfull_bar[as]);
+      if (elect_one()) umma_commit_2cta(&tfull_bar[as]);
+      __syncwarp();
       if (++as == 2) { as = 0; aph ^= 1; }
     }
   } else if (warp >= 4) {
