@@ -81,7 +81,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (threadIdx.x == 0) {
+  if (warp == 0) {
     // ------------------------------------------------ TMA producer
     int s = 0;
     uint32_t ph = 0;
@@ -93,15 +93,18 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         mbar_wait(&empty_bar[s], ph ^ 1);
         uint8_t* a_dst = tiles + s * Cfg::kStageBytes;
         uint8_t* b_dst = a_dst + Cfg::kABytes;
-        mbar_expect_tx(&full_bar[s], Cfg::kStageBytes);
-        if (p.conv_cb_per_tap) {      // implicit 3x3 conv: 128 rows = 8 image rows x 16 columns of sequence tm / 2
-          const int tap = kb / p.conv_cb_per_tap, cb = kb % p.conv_cb_per_tap;
-          tma_load_4d(a_dst, &tmA, &full_bar[s], g * p.conv_cin_stride + cb * BK, tap % 3 - 1, (tm & 1) * 8 + tap / 3 - 1,
-                      tm >> 1);
-        } else {
-          tma_load_3d(a_dst, &tmA, &full_bar[s], kb * BK, tm * BM, g);
+        if (elect_one()) {             // warp-uniform loop, one elected lane issues
+          mbar_expect_tx(&full_bar[s], Cfg::kStageBytes);
+          if (p.conv_cb_per_tap) {    // implicit 3x3 conv: 128 rows = 8 image rows x 16 columns of sequence tm / 2
+            const int tap = kb / p.conv_cb_per_tap, cb = kb % p.conv_cb_per_tap;
+            tma_load_4d(a_dst, &tmA, &full_bar[s], g * p.conv_cin_stride + cb * BK, tap % 3 - 1, (tm & 1) * 8 + tap / 3 - 1,
+                        tm >> 1);
+          } else {
+            tma_load_3d(a_dst, &tmA, &full_bar[s], kb * BK, tm * BM, g);
+          }
+          tma_load_3d(b_dst, &tmB, &full_bar[s], kb * BK, tn * BN, g);
         }
-        tma_load_3d(b_dst, &tmB, &full_bar[s], kb * BK, tn * BN, g);
+        __syncwarp();
         if (++s == Cfg::kStages) { s = 0; ph ^= 1; }
       }
     }

@@ -136,8 +136,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (threadIdx.x == 0) {
-    // ------------------------------------------------ TMA producer (both CTAs)
+  if (warp == 0) {
+    // ------------------------------------------------ TMA producer (both CTAs): warp-uniform loop, one elected lane issues
     int s = 0;
     uint32_t ph = 0;
     for (int t = cluster_id; t < num_tiles; t += num_clusters) {
@@ -147,15 +147,18 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         mbar_wait(&empty_bar[s], ph ^ 1);
         uint8_t* a_dst = tiles + s * kStageBytes;
         uint8_t* b_dst = a_dst + kABytes;
-        if (leader) mbar_expect_tx(&full_bar[s], 2 * kStageBytes);
         const uint32_t bar = mapa_cta(smem_u32(&full_bar[s]), 0);
-        if (p.conv_cb_per_tap) {      // implicit 3x3 conv: the pair tile is one sequence's 16 x 16 map, 8 rows per CTA
-          const int tap = kb / p.conv_cb_per_tap, cb = kb % p.conv_cb_per_tap;
-          tma_load_4d_2cta(a_dst, &tmA, bar, cb * BK, tap % 3 - 1, (int)rank * 8 + tap / 3 - 1, tm);
-        } else {
-          tma_load_3d_2cta(a_dst, &tmA, bar, kb * BK, tm * 2 * BM + (int)rank * BM, 0);
+        if (elect_one()) {
+          if (leader) mbar_expect_tx(&full_bar[s], 2 * kStageBytes);
+          if (p.conv_cb_per_tap) {    // implicit 3x3 conv: the pair tile is one sequence's 16 x 16 map, 8 rows per CTA
+            const int tap = kb / p.conv_cb_per_tap, cb = kb % p.conv_cb_per_tap;
+            tma_load_4d_2cta(a_dst, &tmA, bar, cb * BK, tap % 3 - 1, (int)rank * 8 + tap / 3 - 1, tm);
+          } else {
+            tma_load_3d_2cta(a_dst, &tmA, bar, kb * BK, tm * 2 * BM + (int)rank * BM, 0);
+          }
+          tma_load_3d_2cta(b_dst, &tmB, bar, kb * BK, tn * BN + (int)rank * (BN / 2), 0);
         }
-        tma_load_3d_2cta(b_dst, &tmB, bar, kb * BK, tn * BN + (int)rank * (BN / 2), 0);
+        __syncwarp();
         if (++s == kStages) { s = 0; ph ^= 1; }
       }
     }
