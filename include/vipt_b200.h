@@ -27,7 +27,7 @@ const char* vipt_last_error(void);
 
 /* C = epi(A W^T + bias):  A (M,K) fp16 row-major lda, W (N,K) fp16 row-major ldw  (nn.Linear layout,
  * ViPT/lib/models/layers/attn.py:37,53).  epi: 0 bias->fp16, 1 bias+GELU(erf)->fp16, 2 bias+ReLU->fp16,
- * 3 bias->fp32, 4 resid+bias->fp32.  bn: N tile (256/128/64/32).  K % 64 == 0, N % bn == 0. */
+ * 3 bias->fp32, 4 resid+bias->fp32.  bn: N tile (256/128/64/32), or 512 / 640 for the 2-CTA kernel with 256- / 128-wide pair tiles.  K % 64 == 0, N % tile == 0. */
 int vipt_op_gemm(const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, int bn, int epi,
                  void* out, int64_t ldc, const float* bias, const float* resid, void* stream);
 

@@ -26,7 +26,7 @@ const char* vipt_last_error(void) { return g_err; }
 int vipt_op_gemm(const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, int bn, int epi,
                  void* out, int64_t ldc, const float* bias, const float* resid, void* stream) {
   vipt::GemmOp op;
-  int r = bn == 512 ? vipt::gemm2_plan(&op, A, lda, W, ldw, M, N, K, epi, out, ldc, bias)
+  int r = (bn == 512 || bn == 640) ? vipt::gemm2_plan(&op, A, lda, W, ldw, M, N, K, epi, out, ldc, bias, bn == 640 ? -1 : 0)
                     : vipt::gemm_plan(&op, A, lda, 0, W, ldw, 0, 1, M, N, K, bn, epi, out, ldc, 0, 0, bias, resid);
   if (r) { set_err("gemm_plan failed"); return r; }
   r = vipt::gemm_launch(op, num_sms(), (cudaStream_t)stream);

@@ -88,7 +88,7 @@ int Engine::finalize_buffers() {
   auto plan_lin = [&](GemmOp* op, const void* A, int64_t lda, const void* W, int M, int N, int K, int epi, void* out,
                       const float* bias) -> int {
     const int pair_tiles = ((M + 255) / 256) * (N / 256);
-    if (pair_tiles >= num_sms / 2) return gemm2_plan(op, A, lda, W, K, M, N, K, epi, out, N, bias);
+    if (pair_tiles >= num_sms / 2) return gemm2_plan(op, A, lda, W, K, M, N, K, epi, out, N, bias, num_sms / 2);
     const int mt = (M + 127) / 128;
     int bn = 128;
     while (bn > 32 && mt * (N / bn) < num_sms) bn >>= 1;

@@ -287,7 +287,8 @@ static int launch_bn(const GemmOp& op, int num_sms, cudaStream_t st) {
 
 int gemm_launch(const GemmOp& op, int num_sms, cudaStream_t st) {
   switch (op.bn) {
-    case 512: return gemm2_launch(op, num_sms, st);
+    case 512:
+    case 640: return gemm2_launch(op, num_sms, st);
     case 256: return launch_bn<256>(op, num_sms, st);
     case 128: return launch_bn<128>(op, num_sms, st);
     case 64: return launch_bn<64>(op, num_sms, st);

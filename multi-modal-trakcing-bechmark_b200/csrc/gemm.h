@@ -50,7 +50,7 @@ int gemm2_plan_conv(GemmOp* op, const void* feat, int c_total, int cin, const vo
 int gemm_launch(const GemmOp& op, int num_sms, cudaStream_t st);   // dispatches 2-CTA plans (bn == 512) to gemm2
 // 2-CTA (cta_group::2) kernel for large single-group GEMMs with N % 256 == 0 (gemm2.cu)
 int gemm2_plan(GemmOp* op, const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, int epi,
-               void* out, int64_t ldc, const float* bias);
+               void* out, int64_t ldc, const float* bias, int num_clusters = 0);
 int gemm2_launch(const GemmOp& op, int num_sms, cudaStream_t st);
 
 }  // namespace vipt

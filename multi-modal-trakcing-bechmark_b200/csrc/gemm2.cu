@@ -19,17 +19,21 @@ namespace vipt {
 
 namespace g2 {
 constexpr int BM = 128;            // rows per CTA (256 per pair)
-constexpr int BN = 256;            // columns per pair tile
 constexpr int BK = 64;
-constexpr int kStages = 5;
 constexpr int kSlabCols = 64;                        // epilogue slab: 128 rows x 64 fp16 = 16 KB, SW128
 constexpr int kSlabBytes = BM * kSlabCols * 2;
 constexpr int kABytes = BM * BK * 2;
-constexpr int kBBytes = (BN / 2) * BK * 2;
-constexpr int kStageBytes = kABytes + kBBytes;
 constexpr int kThreads = 384;          // warp 0 TMA, 1 MMA, 2 TMEM alloc, 4..11 epilogue (2 per TMEM lane group)
 constexpr int kEpiThreads = 256;
-constexpr int kSmemBytes = 1024 + kStages * kStageBytes + 2 * kSlabBytes + BN * 4 + (2 * kStages + 4) * 8 + 16;
+// BN = columns per pair tile: 256, or 128 for the N = 768 layers (proj, fc2), whose 3 x tiles_m grid of
+// 256-wide tiles leaves the last wave of the persistent loop a third empty
+template <int BN>
+struct Cfg {
+  static constexpr int kStages = BN == 256 ? 5 : 7;
+  static constexpr int kBBytes = (BN / 2) * BK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kSmemBytes = 1024 + kStages * kStageBytes + 2 * kSlabBytes + BN * 4 + (2 * kStages + 4) * 8 + 16;
+};
 }  // namespace g2
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
@@ -83,11 +87,12 @@ __device__ __forceinline__ void umma_commit_2cta(uint64_t* bar) {     // arrives
       : "memory");
 }
 
-template <int EPI>
+template <int EPI, int BN>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(g2::kThreads, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
              const __grid_constant__ CUtensorMap tmC, GemmParams p) {
   using namespace g2;
+  constexpr int kStages = Cfg<BN>::kStages, kStageBytes = Cfg<BN>::kStageBytes;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* tiles = smem;
@@ -273,35 +278,41 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   }
 }
 
-template <int EPI>
+template <int EPI, int BN>
 static int launch2_t(const GemmOp& op, int num_sms, cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
-    if (cudaFuncSetAttribute(gemm2_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, g2::kSmemBytes) != cudaSuccess)
+    if (cudaFuncSetAttribute(gemm2_kernel<EPI, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, g2::Cfg<BN>::kSmemBytes) !=
+        cudaSuccess)
       return VIPT_ERR_LAUNCH;
     attr_set = true;
   }
-  const int tiles = ((op.p.M + 255) / 256) * (op.p.N / 256);
+  const int tiles = ((op.p.M + 255) / 256) * (op.p.N / BN);
   int grid = 2 * tiles;
   const int cap = num_sms & ~1;
   if (grid > cap) grid = cap;
-  gemm2_kernel<EPI><<<grid, g2::kThreads, g2::kSmemBytes, st>>>(op.tmA, op.tmB, op.tmC, op.p);
+  gemm2_kernel<EPI, BN><<<grid, g2::kThreads, g2::Cfg<BN>::kSmemBytes, st>>>(op.tmA, op.tmB, op.tmC, op.p);
   return cudaGetLastError() == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
 }
 
 int gemm2_launch(const GemmOp& op, int num_sms, cudaStream_t st) {
+  const bool narrow = op.bn == 640;
   switch (op.epi) {
-    case EPI_BIAS_F16: return launch2_t<EPI_BIAS_F16>(op, num_sms, st);
-    case EPI_GELU_F16: return launch2_t<EPI_GELU_F16>(op, num_sms, st);
-    case EPI_RELU_F16: return launch2_t<EPI_RELU_F16>(op, num_sms, st);
+    case EPI_BIAS_F16: return narrow ? launch2_t<EPI_BIAS_F16, 128>(op, num_sms, st) : launch2_t<EPI_BIAS_F16, 256>(op, num_sms, st);
+    case EPI_GELU_F16: return narrow ? launch2_t<EPI_GELU_F16, 128>(op, num_sms, st) : launch2_t<EPI_GELU_F16, 256>(op, num_sms, st);
+    case EPI_RELU_F16: return narrow ? launch2_t<EPI_RELU_F16, 128>(op, num_sms, st) : launch2_t<EPI_RELU_F16, 256>(op, num_sms, st);
   }
   return VIPT_ERR_ARG;
 }
 
 // same operand conventions as gemm_plan, single group, N % 256 == 0; W box = 128 rows (half tile per CTA)
 int gemm2_plan(GemmOp* op, const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, int epi,
-               void* out, int64_t ldc, const float* bias) {
-  if (K % g2::BK != 0 || N % g2::BN != 0 || M <= 0 || epi == EPI_RESID_F32 || epi == EPI_BIAS_F32) return VIPT_ERR_ARG;
+               void* out, int64_t ldc, const float* bias, int num_clusters) {
+  if (K % g2::BK != 0 || N % 128 != 0 || M <= 0 || epi == EPI_RESID_F32 || epi == EPI_BIAS_F32) return VIPT_ERR_ARG;
+  // 128-wide pair tiles only when N is not a multiple of 256 (or forced, num_clusters < 0).  Choosing them for the
+  // N = 768 layers to shorten the last wave (480 half-tiles = 3.5 rounds instead of 4) was measured and lost:
+  // linear GEMMs 2.25 -> 2.32 ms per step, the narrow tile moves 1.5x the operand bytes per flop.
+  const int bn = (N % 256 != 0 || num_clusters < 0) ? 128 : 256;
   if ((ldc * 2) % 16 != 0 || (reinterpret_cast<uintptr_t>(out) & 15)) return VIPT_ERR_ARG;
   if ((lda * 2) % 16 != 0 || (ldw * 2) % 16 != 0 || (reinterpret_cast<uintptr_t>(A) & 15) ||
       (reinterpret_cast<uintptr_t>(W) & 15))
@@ -313,7 +324,7 @@ int gemm2_plan(GemmOp* op, const void* A, int64_t lda, const void* W, int64_t ld
   if (r) return r;
   uint64_t db[3] = {(uint64_t)K, (uint64_t)N, 1};
   uint64_t sb[2] = {(uint64_t)ldw * 2, (uint64_t)N * ldw * 2};
-  uint32_t bb[3] = {g2::BK, g2::BN / 2, 1};
+  uint32_t bb[3] = {g2::BK, (uint32_t)bn / 2, 1};
   r = make_tmap_f16(&op->tmB, W, 3, db, sb, bb);
   if (r) return r;
   uint64_t dc[3] = {(uint64_t)N, (uint64_t)M, 1};
@@ -325,7 +336,7 @@ int gemm2_plan(GemmOp* op, const void* A, int64_t lda, const void* W, int64_t ld
   op->p.out = out; op->p.ldc = ldc; op->p.out_group_stride = 0; op->p.out_group_col = 0;
   op->p.bias = bias; op->p.resid = nullptr;
   op->p.conv_cb_per_tap = 0; op->p.conv_cin_stride = 0;
-  op->bn = 512;      // marks a 2-CTA plan
+  op->bn = bn == 256 ? 512 : 640;      // marks a 2-CTA plan (256- / 128-wide pair tiles)
   op->epi = epi;
   return VIPT_OK;
 }
@@ -335,7 +346,8 @@ int gemm2_plan_conv(GemmOp* op, const void* feat, int c_total, int cin, const vo
   if (cin % g2::BK != 0 || (c_total * 2) % 16 != 0) return VIPT_ERR_ARG;
   const int K = 9 * cin;
   // the plain plan builds valid W / C maps; its A map (a (M, K) view that does not exist) is replaced below
-  int r = gemm2_plan(op, W, K, W, K, B * 256, N, K, epi, out, ldc, bias);
+  int r = gemm2_plan(op, W, K, W, K, B * 256, N, K, epi, out, ldc, bias, 0);
+  if (!r && op->bn != 512) return VIPT_ERR_ARG;
   if (r) return r;
   uint64_t d[4] = {(uint64_t)c_total, 16, 16, (uint64_t)B};
   uint64_t sb[3] = {(uint64_t)c_total * 2, (uint64_t)16 * c_total * 2, (uint64_t)256 * c_total * 2};
