@@ -78,15 +78,19 @@ int vipt_engine_track_enqueue(void* engine, const void* frame_ptrs_dev, int use_
 /* copies the latest boxes (B,4) [x,y,w,h] and best scores (B) to host memory and synchronises the stream. */
 int vipt_engine_results(void* engine, double* boxes_host, float* scores_host, void* stream);
 /* HOST-frame variants (the reference hands ViPTTrack host ndarrays, vipt.py:41,64): frames are B host pointers to
- * uint8 (H,W,6) images (pinned memory for asynchronous copies).  init_host uploads the whole frames into
- * engine-owned device buffers; track_host uploads only the rectangle the search crop can read
- * (processing_utils.py:32-47, evaluated from the host mirror of the box state that vipt_engine_results keeps
- * current; the whole frame when the mirror is stale) and enqueues one step.  bytes_copied (optional) receives the
- * number of bytes uploaded.  set_state overrides the box state (teacher-forced evaluation). */
+ * uint8 (H,W,6) images.  init_host uploads the whole frames into engine-owned device buffers; track_host brings in
+ * only the rectangle the search crop can read (processing_utils.py:32-47) and enqueues one step.  Page-locked
+ * frames (cudaHostAlloc / cudaHostRegister / torch pin_memory): one gather kernel reads all B rectangles straight
+ * from host memory, the rectangle evaluated on the device from the box state, so up to 4 steps may be enqueued
+ * before their results are collected; bytes_copied is then -1 at enqueue and reported by collect.  Pageable frames:
+ * one 2-D copy per sequence, rectangle from the host mirror of the state (whole frame when the mirror is stale).
+ * collect returns the boxes / scores of the OLDEST uncollected track_host step (VIPT_ERR_STATE when there is none).
+ * set_state overrides the box state (teacher-forced evaluation). */
 int vipt_engine_init_host(void* engine, const void* const* host_frames, const int* hw_host, const double* boxes_host,
                           void* stream);
 int vipt_engine_track_host(void* engine, const void* const* host_frames, int use_graph, int64_t* bytes_copied,
                            void* stream);
+int vipt_engine_collect(void* engine, double* boxes_host, float* scores_host, int64_t* bytes_copied);
 int vipt_engine_set_state(void* engine, const double* boxes_host, void* stream);
 /* one un-graphed step with a CUDA-event pair around every kernel launch; sums (ms) and launch counts per
  * kernel class: 0 linear GEMMs, 1 head conv GEMMs, 2 attention, 3 prompt blocks, 4 LayerNorm/CE/final,

@@ -33,6 +33,7 @@ SIGNATURES = {
     "vipt_engine_track_enqueue": (c_int, [c_void_p, c_void_p, c_int, c_void_p]),
     "vipt_engine_init_host": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "vipt_engine_track_host": (c_int, [c_void_p, c_void_p, c_int, ctypes.POINTER(c_i64), c_void_p]),
+    "vipt_engine_collect": (c_int, [c_void_p, c_void_p, c_void_p, ctypes.POINTER(c_i64)]),
     "vipt_engine_set_state": (c_int, [c_void_p, c_void_p, c_void_p]),
     "vipt_engine_profile_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "vipt_engine_results": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),

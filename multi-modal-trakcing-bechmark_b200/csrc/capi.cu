@@ -112,7 +112,9 @@ int vipt_engine_results(void* ev, double* boxes_host, float* scores_host, void* 
   }
   if (herr == VIPT_ERR_SMALL_BOX) set_err("Too small bounding box.");
   e->host_state.assign(boxes_host, boxes_host + 4 * e->B);     // mirror for the ROI uploads (engine3.cu)
+  e->spec_state = e->host_state;
   e->mirror_valid = true;
+  e->res_pending = 0;            // the latest state has been read: earlier uncollected steps are dropped
   return herr;
 }
 int vipt_engine_init_host(void* e, const void* const* host_frames, const int* hw_host, const double* boxes_host,
@@ -125,6 +127,13 @@ int vipt_engine_init_host(void* e, const void* const* host_frames, const int* hw
 int vipt_engine_track_host(void* e, const void* const* host_frames, int use_graph, int64_t* bytes_copied, void* stream) {
   if (!e || !host_frames) return VIPT_ERR_ARG;
   return ((vipt::Engine*)e)->track_host(host_frames, use_graph != 0, bytes_copied, (cudaStream_t)stream);
+}
+int vipt_engine_collect(void* e, double* boxes_host, float* scores_host, int64_t* bytes_copied) {
+  if (!e || !boxes_host || !scores_host) return VIPT_ERR_ARG;
+  int r = ((vipt::Engine*)e)->collect(boxes_host, scores_host, bytes_copied);
+  if (r == VIPT_ERR_SMALL_BOX) set_err("Too small bounding box.");
+  else if (r == VIPT_ERR_STATE) set_err("no enqueued host-frame step to collect");
+  return r;
 }
 int vipt_engine_set_state(void* e, const double* boxes_host, void* stream) {
   if (!e || !boxes_host) return VIPT_ERR_ARG;

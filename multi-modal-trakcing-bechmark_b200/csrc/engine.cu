@@ -30,6 +30,13 @@ Engine::~Engine() {
   if (graph_exec) cudaGraphExecDestroy(graph_exec);
   for (void* p : allocs) cudaFree(p);
   for (void* p : own_frames) cudaFree(p);
+  if (res_host) cudaFreeHost(res_host);
+  if (side_stream) cudaStreamDestroy(side_stream);
+  if (spec_ev) cudaEventDestroy(spec_ev);
+  for (cudaEvent_t e : set_free_ev)
+    if (e) cudaEventDestroy(e);
+  for (cudaEvent_t e : res_ev)
+    if (e) cudaEventDestroy(e);
 }
 
 void* Engine::dalloc(size_t bytes) {

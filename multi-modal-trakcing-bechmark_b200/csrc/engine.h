@@ -75,11 +75,35 @@ struct Engine {
   int* gi_final = nullptr;
 
   // host-frame path (engine3.cu): engine-owned frame buffers + host mirror of the box state
-  std::vector<void*> own_frames;
-  const uint8_t** own_ptrs_dev = nullptr;
+  std::vector<void*> own_frames;           // [2][B]: two sets, a step uses set (step & 1)
+  const uint8_t** own_ptrs_dev = nullptr;  // the set the NEXT enqueued step reads (written in stream order)
+  int ptrs_set = 0;                        // set own_ptrs_dev holds after the work enqueued so far
+  long host_step = 0;
+  cudaStream_t side_stream = nullptr;      // speculative gathers run here, next to the previous step
+  cudaEvent_t set_free_ev[2] = {};         // recorded after the last step that read frame set i
+  cudaEvent_t spec_ev = nullptr;
   std::vector<int> host_hw;
   std::vector<double> host_state;
   bool mirror_valid = false;
+  // zero-copy gather: the device-visible addresses of the B host frames travel as a kernel parameter
+  static constexpr int kRoiSlots = 4;      // steps that may be enqueued before their results are collected
+  static constexpr int kRoiMaxB = 128;
+  struct RoiSrc {
+    const uint8_t* p[kRoiMaxB];
+  };
+  struct RoiHave {                         // rectangle already present in the frame set: x_lo, x_hi, y_lo, y_hi
+    int r[kRoiMaxB][4];
+  };
+  std::vector<double> spec_state;          // boxes of the last collected step (speculative uploads)
+  uint8_t** own_tab_dev = nullptr;         // [2 sets][B] frame buffers, device copy of own_frames
+  int* roi_bytes_dev = nullptr;            // [2][B] bytes gathered per sequence in the last step: speculative, exact
+  // per-step results of the host-frame path: pinned ring, one slot per enqueued step (vipt_engine_collect)
+  uint8_t* res_host = nullptr;             // [kRoiSlots][boxes B*32 | scores B*4 | roi bytes 2*B*4 | err 4 | pad]
+  cudaEvent_t res_ev[kRoiSlots] = {};
+  long long res_host_bytes[kRoiSlots] = {};   // >= 0: bytes copied, known on the host at enqueue (pageable path)
+  int res_head = 0, res_pending = 0;
+  size_t res_slot_bytes() const { return (size_t)B * 44 + 16; }
+  int collect(double* boxes_host, float* scores_host, int64_t* bytes_copied);
   int init_host(const void* const* host_frames, const int* hw_host, const double* boxes_host, cudaStream_t st);
   int track_host(const void* const* host_frames, bool use_graph, int64_t* bytes_copied, cudaStream_t st);
   int set_state(const double* boxes_host, cudaStream_t st);

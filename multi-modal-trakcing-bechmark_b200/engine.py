@@ -122,6 +122,15 @@ class NativeEngine:
                    "vipt_engine_track_host")
         return n.value
 
+    def collect(self):
+        """-> (boxes (B,4) f64, scores (B,) f32, bytes uploaded) of the oldest uncollected track_host step."""
+        boxes = np.empty((self.batch, 4), np.float64)
+        scores = np.empty((self.batch,), np.float32)
+        n = ctypes.c_int64(0)
+        _lib.check(self.L.vipt_engine_collect(self.h, boxes.ctypes.data_as(ctypes.c_void_p),
+                                              scores.ctypes.data_as(ctypes.c_void_p), ctypes.byref(n)), "vipt_engine_collect")
+        return boxes, scores, n.value
+
     def set_state(self, boxes):
         bx = np.ascontiguousarray(np.asarray(boxes, np.float64).reshape(self.batch, 4))
         _lib.check(self.L.vipt_engine_set_state(self.h, bx.ctypes.data_as(ctypes.c_void_p), self._sp()),

@@ -66,6 +66,7 @@ class BatchedViPTTracker:
         self.frame_id = 0
         self.state = boxes.copy()
         self.h2d_bytes = 0
+        self._pending_host = 0
 
     def set_state(self, boxes):
         """Override the box state of every sequence (teacher-forced evaluation)."""
@@ -77,7 +78,10 @@ class BatchedViPTTracker:
             views = [self._host_view(im) for im in images]
             assert [v[1] for v in views] == self._hw, "frame size changed within a sequence"
             # only the rectangle the search crop reads travels to the device (csrc/engine3.cu)
-            self.h2d_bytes = self.engine.track_host([v[0] for v in views], self.use_graph, keepalive=[v[2] for v in views])
+            n = self.engine.track_host([v[0] for v in views], self.use_graph, keepalive=[v[2] for v in views])
+            if n >= 0:
+                self.h2d_bytes = n
+            self._pending_host += 1
         else:
             frames = [im if (isinstance(im, torch.Tensor) and im.is_cuda) else
                       torch.from_numpy(np.ascontiguousarray(im)).to(self.engine.device) for im in images]
@@ -88,11 +92,24 @@ class BatchedViPTTracker:
             self.engine.track_enqueue(ptrs, self.use_graph)
         self.frame_id += 1
 
-    def track(self, images):
-        self.track_async(images)
-        boxes, scores = self.engine.results()
+    def collect(self):
+        """Boxes (B,4) and scores (B,) of the oldest step enqueued with track_async(host frames) and not yet collected.
+        With page-locked host frames up to 4 steps may be in flight: enqueue step t+1, then collect step t, so the
+        host never stalls the device (the rectangle of step t+1 is evaluated on the device from step t's boxes)."""
+        if self._pending_host > 0:
+            boxes, scores, n = self.engine.collect()
+            self._pending_host -= 1
+            self.h2d_bytes = n
+        else:
+            boxes, scores = self.engine.results()
         self.state = boxes
         return boxes, scores
+
+    def track(self, images):
+        self.track_async(images)
+        while self._pending_host > 1:            # results of earlier track_async calls nobody collected
+            self.collect()
+        return self.collect()
 
 
 class ViPTTrack:

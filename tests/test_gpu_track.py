@@ -94,26 +94,52 @@ def test_too_small_box_raises():
         trk.initialize([frames[0]], [[5.0, 5.0, 0.0, 3.0]])
 
 
-def test_host_roi_upload_matches_device_frames():
+@pytest.mark.parametrize("pinned", [False, True])
+def test_host_roi_upload_matches_device_frames(pinned):
     """track(host frames) uploads only the search rectangle (csrc/engine3.cu); the boxes must be bit-identical
-    to the path that keeps whole frames on the device, including crops that overhang the frame."""
+    to the path that keeps whole frames on the device, including crops that overhang the frame.
+    pinned=False: pageable ndarrays, one 2-D copy per sequence; pinned=True: page-locked tensors, one zero-copy gather
+    kernel per step (the third frame is an odd-offset view, so source and destination alignments differ)."""
     B, T = 3, 6
     sd = synth.synthetic_state_dict("vipt_deep", 0)
     seqs = [synth.synthetic_sequence(40 + i, T, "rgbt") for i in range(B)]
+    if pinned:
+        def pin(f, odd):
+            flat = torch.empty(f.size + 16, dtype=torch.uint8).pin_memory()
+            v = flat[3:3 + f.size] if odd else flat[:f.size]
+            v.copy_(torch.from_numpy(f).reshape(-1))
+            return v.view(f.shape)
+        seqs = [([pin(f, i == 2) for f in s[0]], s[1]) for i, s in enumerate(seqs)]
+        as_dev = lambda f: f.cuda()
+    else:
+        as_dev = lambda f: torch.from_numpy(f).cuda()
     H, W = seqs[0][0][0].shape[:2]
     boxes0 = [list(seqs[0][1]), [2.0, 3.0, 50.0, 40.0], [W - 45.0, H - 38.0, 60.0, 50.0]]   # interior, two corners
     a = BatchedViPTTracker(sd, B, "vipt_deep", use_graph=False)
     b = BatchedViPTTracker(sd, B, "vipt_deep", use_graph=False)
     a.initialize([s[0][0] for s in seqs], boxes0)
-    b.initialize([torch.from_numpy(s[0][0]).cuda() for s in seqs], boxes0)
+    b.initialize([as_dev(s[0][0]) for s in seqs], boxes0)
     for t in range(1, T):
         ba, sa = a.track([s[0][t] for s in seqs])
-        bb, sb = b.track([torch.from_numpy(s[0][t]).cuda() for s in seqs])
+        bb, sb = b.track([as_dev(s[0][t]) for s in seqs])
         assert 0 < a.h2d_bytes < B * H * W * 6
         np.testing.assert_array_equal(ba, bb)
         np.testing.assert_array_equal(sa, sb)
-    # stale mirror (two steps enqueued without reading results) falls back to whole frames
+    # two steps enqueued without reading results in between
     a.track_async([s[0][1] for s in seqs]); a.track_async([s[0][2] for s in seqs])
-    assert a.h2d_bytes == B * H * W * 6
-    b.track_async([torch.from_numpy(s[0][1]).cuda() for s in seqs]); b.track_async([torch.from_numpy(s[0][2]).cuda() for s in seqs])
-    np.testing.assert_array_equal(a.engine.results()[0], b.engine.results()[0])
+    b.track_async([as_dev(s[0][1]) for s in seqs])
+    b1 = b.engine.results()[0]
+    b.track_async([as_dev(s[0][2]) for s in seqs])
+    b2 = b.engine.results()[0]
+    if pinned:       # rectangles evaluated on the device from the current state: both steps stay partial uploads
+        a1, _ = a.collect()
+        assert 0 < a.h2d_bytes < B * H * W * 6
+        a2, _ = a.collect()
+        assert 0 < a.h2d_bytes < B * H * W * 6
+        np.testing.assert_array_equal(a1, b1)
+        np.testing.assert_array_equal(a2, b2)
+        with pytest.raises(RuntimeError):
+            a.engine.collect()                   # nothing left to collect
+    else:            # stale host mirror: the second step falls back to whole frames
+        assert a.h2d_bytes == B * H * W * 6
+        np.testing.assert_array_equal(a.engine.results()[0], b2)
