@@ -66,9 +66,10 @@ struct Engine {
   const uint8_t** frame_ptrs;         // (B) device array of frame pointers
 
   // plans (TMA descriptors encoded once)
-  GemmOp g_pe, g_qkv[kDepth], g_proj[kDepth], g_fc1[kDepth], g_fc2[kDepth];
+  GemmOp g_pe, g_pe2[2], g_qkv[kDepth], g_proj[kDepth], g_fc1[kDepth], g_fc2[kDepth];
   GemmOp g_c1, g_c2, g_c3, g_c4;
   AttnOp a_op[kDepth];
+  bool pe_pair = false;      // patch embed on the 2-CTA kernel (one launch per modality)
   int n_mlp[kDepth];         // tokens in layer i's MLP (after CE)
 
   float* x_final = nullptr;   // residual stream / index list after the last block (debug, forward outputs)

@@ -81,8 +81,16 @@ int Engine::finalize_buffers() {
   }
   // ---- GEMM / attention plans
   const int M0 = B * kLensFull;
-  RET(gemm_plan(&g_pe, apatch, 768, (int64_t)M0 * 768, w_pe, 768, 768 * 768, 2, M0, 768, 768, 256, EPI_BIAS_F32, E, 768,
-                (int64_t)M0 * 768, 0, b_pe, nullptr));
+  // patch embed of both modalities (fp32 out): two launches of the 2-CTA kernel at large batch, else one grouped launch
+  pe_pair = ((M0 + 255) / 256) * 3 >= num_sms / 2;
+  if (pe_pair) {
+    for (int g = 0; g < 2; ++g)
+      RET(gemm2_plan(&g_pe2[g], apatch + (size_t)g * M0 * 768, 768, w_pe + (size_t)g * 768 * 768, 768, M0, 768, 768, EPI_BIAS_F32,
+                     E + (size_t)g * M0 * 768, 768, b_pe + g * 768, num_sms / 2));
+  } else {
+    RET(gemm_plan(&g_pe, apatch, 768, (int64_t)M0 * 768, w_pe, 768, 768 * 768, 2, M0, 768, 768, 256, EPI_BIAS_F32, E, 768,
+                  (int64_t)M0 * 768, 0, b_pe, nullptr));
+  }
   // Large batches: 2-CTA 256 x 256 tiles.  Small batches (latency mode): the pair kernel would fill only a few
   // SMs, so the single-CTA kernel with narrow N tiles spreads the weight stream over the whole chip.
   auto plan_lin = [&](GemmOp* op, const void* A, int64_t lda, const void* W, int M, int N, int K, int epi, void* out,
@@ -136,7 +144,12 @@ int Engine::run_backbone_head(bool tracking, bool want_feat32, int debug_stop, c
   const size_t RH = (size_t)B * kLensX;
   CK(cudaMemcpyAsync(giA, ident, RH * 4, cudaMemcpyDeviceToDevice, st));
   CK(cudaMemcpyAsync(slot_of_pos, ident, RH * 4, cudaMemcpyDeviceToDevice, st));
-  LAUNCH(K_GEMM, gemm_launch(g_pe, num_sms, st));
+  if (pe_pair) {
+    LAUNCH(K_GEMM, gemm_launch(g_pe2[0], num_sms, st));
+    LAUNCH(K_GEMM, gemm_launch(g_pe2[1], num_sms, st));
+  } else {
+    LAUNCH(K_GEMM, gemm_launch(g_pe, num_sms, st));
+  }
   STAGE_END();   // 1: E
   const float* E0 = E;
   const float* E1 = E + (size_t)B * kLensFull * 768;

@@ -262,10 +262,9 @@ int Engine::track_host(const void* const* host_frames, bool use_graph, int64_t* 
   CK(cudaMemcpyAsync(slot + (size_t)B * 44, err, 4, cudaMemcpyDeviceToHost, st));
   if (!res_ev[res_head]) CK(cudaEventCreateWithFlags(&res_ev[res_head], cudaEventDisableTiming));
   CK(cudaEventRecord(res_ev[res_head], st));
-  if (mapped) {      // frame set, rectangle record and byte counters of this step may be rewritten after this point
-    if (!set_free_ev[set]) CK(cudaEventCreateWithFlags(&set_free_ev[set], cudaEventDisableTiming));
-    CK(cudaEventRecord(set_free_ev[set], st));
-  }
+  // frame set and byte counters of this step may be rewritten after this point (speculative uploads wait for it)
+  if (!set_free_ev[set]) CK(cudaEventCreateWithFlags(&set_free_ev[set], cudaEventDisableTiming));
+  CK(cudaEventRecord(set_free_ev[set], st));
   res_host_bytes[res_head] = total;
   res_head = (res_head + 1) % kRoiSlots;
   ++res_pending;

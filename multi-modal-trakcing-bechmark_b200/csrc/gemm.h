@@ -39,6 +39,8 @@ struct GemmOp {
 
 int make_tmap_f16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                   const uint32_t* box);
+int make_tmap_f32(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                  const uint32_t* box);
 int gemm_plan(GemmOp* op, const void* A, int64_t lda, int64_t a_group_stride, const void* W, int64_t ldw,
               int64_t w_group_stride, int G, int M, int N, int K, int bn, int epi, void* out, int64_t ldc,
               int64_t out_group_stride, int64_t out_group_col, const float* bias, const float* resid);

@@ -29,10 +29,11 @@ constexpr int kEpiThreads = 256;
 // 256-wide tiles leaves the last wave of the persistent loop a third empty
 template <int BN>
 struct Cfg {
-  static constexpr int kStages = BN == 256 ? 5 : 7;
+  static constexpr int kStages = BN == 256 ? 5 : 6;
   static constexpr int kBBytes = (BN / 2) * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kSmemBytes = 1024 + kStages * kStageBytes + 2 * kSlabBytes + BN * 4 + (2 * kStages + 4) * 8 + 16;
+  // 4 staging slabs: 2 for fp16 outputs (double-buffered 64-column slabs), 4 for fp32 outputs (two 32-column slabs per step)
+  static constexpr int kSmemBytes = 1024 + kStages * kStageBytes + 4 * kSlabBytes + BN * 4 + (2 * kStages + 4) * 8 + 16;
 };
 }  // namespace g2
 
@@ -97,7 +98,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* tiles = smem;
   uint8_t* slab = smem + kStages * kStageBytes;            // 2 x 16 KB output staging (TMA store source)
-  float* bias_s = reinterpret_cast<float*>(slab + 2 * kSlabBytes);
+  float* bias_s = reinterpret_cast<float*>(slab + 4 * kSlabBytes);
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(bias_s + BN);
   uint64_t* empty_bar = full_bar + kStages;
   uint64_t* tfull_bar = empty_bar + kStages;
@@ -222,7 +223,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
       tmem_ld32(taddr0, v);
 #pragma unroll 1
       for (int sl = 0; sl < BN / kSlabCols; ++sl) {
-        uint8_t* buf = slab + (sl & 1) * kSlabBytes;
+        // fp16 outputs: one 64-column slab per step; fp32 outputs: each warp set fills its own 32-column slab
+        uint8_t* buf = slab + (EPI == EPI_BIAS_F32 ? ((sl & 1) * 2 + hh) : (sl & 1)) * kSlabBytes;
         const uint32_t prow = smem_u32(buf) + r * 128;
         const uint32_t brow = bias_u32 + (sl * kSlabCols + hh * 32) * 4;
         float f[32];
@@ -242,11 +244,18 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
 #pragma unroll
           for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
         }
+        if (EPI == EPI_BIAS_F32) {
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const int chunk = (hh * 4 + q) ^ (r & 7);          // 128-byte swizzle, matches tmC
-          sts128(prow + chunk * 16, pack_op2(f[q * 8 + 0], f[q * 8 + 1]), pack_op2(f[q * 8 + 2], f[q * 8 + 3]),
-                 pack_op2(f[q * 8 + 4], f[q * 8 + 5]), pack_op2(f[q * 8 + 6], f[q * 8 + 7]));
+          for (int q = 0; q < 8; ++q)                          // 128-byte rows of 32 fp32, 128-byte swizzle
+            sts128(prow + ((q ^ (r & 7)) * 16), __float_as_uint(f[q * 4 + 0]), __float_as_uint(f[q * 4 + 1]),
+                   __float_as_uint(f[q * 4 + 2]), __float_as_uint(f[q * 4 + 3]));
+        } else {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const int chunk = (hh * 4 + q) ^ (r & 7);          // 128-byte swizzle, matches tmC
+            sts128(prow + chunk * 16, pack_op2(f[q * 8 + 0], f[q * 8 + 1]), pack_op2(f[q * 8 + 2], f[q * 8 + 3]),
+                   pack_op2(f[q * 8 + 4], f[q * 8 + 5]), pack_op2(f[q * 8 + 6], f[q * 8 + 7]));
+          }
         }
         fence_proxy_async_smem();
         // one barrier per slab: before it, the issuing thread makes sure the PREVIOUS store has drained its
@@ -254,10 +263,19 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         if (et == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
         asm volatile("bar.sync 1, 256;" ::: "memory");
         if (et == 0) {
-          asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
-                       ::"l"(reinterpret_cast<uint64_t>(&tmC)), "r"(smem_u32(buf)), "r"(n0 + sl * kSlabCols), "r"(row0),
-                       "r"(0)
-                       : "memory");
+          if (EPI == EPI_BIAS_F32) {
+#pragma unroll
+            for (int h2 = 0; h2 < 2; ++h2)
+              asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+                           ::"l"(reinterpret_cast<uint64_t>(&tmC)), "r"(smem_u32(slab + ((sl & 1) * 2 + h2) * kSlabBytes)),
+                             "r"(n0 + sl * kSlabCols + h2 * 32), "r"(row0), "r"(0)
+                           : "memory");
+          } else {
+            asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+                         ::"l"(reinterpret_cast<uint64_t>(&tmC)), "r"(smem_u32(buf)), "r"(n0 + sl * kSlabCols), "r"(row0),
+                         "r"(0)
+                         : "memory");
+          }
           asm volatile("cp.async.bulk.commit_group;" ::: "memory");
         }
       }
@@ -301,6 +319,7 @@ int gemm2_launch(const GemmOp& op, int num_sms, cudaStream_t st) {
     case EPI_BIAS_F16: return narrow ? launch2_t<EPI_BIAS_F16, 128>(op, num_sms, st) : launch2_t<EPI_BIAS_F16, 256>(op, num_sms, st);
     case EPI_GELU_F16: return narrow ? launch2_t<EPI_GELU_F16, 128>(op, num_sms, st) : launch2_t<EPI_GELU_F16, 256>(op, num_sms, st);
     case EPI_RELU_F16: return narrow ? launch2_t<EPI_RELU_F16, 128>(op, num_sms, st) : launch2_t<EPI_RELU_F16, 256>(op, num_sms, st);
+    case EPI_BIAS_F32: return narrow ? launch2_t<EPI_BIAS_F32, 128>(op, num_sms, st) : launch2_t<EPI_BIAS_F32, 256>(op, num_sms, st);
   }
   return VIPT_ERR_ARG;
 }
@@ -308,12 +327,13 @@ int gemm2_launch(const GemmOp& op, int num_sms, cudaStream_t st) {
 // same operand conventions as gemm_plan, single group, N % 256 == 0; W box = 128 rows (half tile per CTA)
 int gemm2_plan(GemmOp* op, const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, int epi,
                void* out, int64_t ldc, const float* bias, int num_clusters) {
-  if (K % g2::BK != 0 || N % 128 != 0 || M <= 0 || epi == EPI_RESID_F32 || epi == EPI_BIAS_F32) return VIPT_ERR_ARG;
+  if (K % g2::BK != 0 || N % 128 != 0 || M <= 0 || epi == EPI_RESID_F32) return VIPT_ERR_ARG;
   // 128-wide pair tiles only when N is not a multiple of 256 (or forced, num_clusters < 0).  Choosing them for the
   // N = 768 layers to shorten the last wave (480 half-tiles = 3.5 rounds instead of 4) was measured and lost:
   // linear GEMMs 2.25 -> 2.32 ms per step, the narrow tile moves 1.5x the operand bytes per flop.
   const int bn = (N % 256 != 0 || num_clusters < 0) ? 128 : 256;
-  if ((ldc * 2) % 16 != 0 || (reinterpret_cast<uintptr_t>(out) & 15)) return VIPT_ERR_ARG;
+  const int osz = epi == EPI_BIAS_F32 ? 4 : 2;
+  if ((ldc * osz) % 16 != 0 || (reinterpret_cast<uintptr_t>(out) & 15)) return VIPT_ERR_ARG;
   if ((lda * 2) % 16 != 0 || (ldw * 2) % 16 != 0 || (reinterpret_cast<uintptr_t>(A) & 15) ||
       (reinterpret_cast<uintptr_t>(W) & 15))
     return VIPT_ERR_ARG;
@@ -328,9 +348,9 @@ int gemm2_plan(GemmOp* op, const void* A, int64_t lda, const void* W, int64_t ld
   r = make_tmap_f16(&op->tmB, W, 3, db, sb, bb);
   if (r) return r;
   uint64_t dc[3] = {(uint64_t)N, (uint64_t)M, 1};
-  uint64_t sc[2] = {(uint64_t)ldc * 2, (uint64_t)M * ldc * 2};
-  uint32_t bc[3] = {g2::kSlabCols, g2::BM, 1};
-  r = make_tmap_f16(&op->tmC, out, 3, dc, sc, bc);
+  uint64_t sc[2] = {(uint64_t)ldc * osz, (uint64_t)M * ldc * osz};
+  uint32_t bc[3] = {(uint32_t)(epi == EPI_BIAS_F32 ? 32 : g2::kSlabCols), g2::BM, 1};
+  r = epi == EPI_BIAS_F32 ? make_tmap_f32(&op->tmC, out, 3, dc, sc, bc) : make_tmap_f16(&op->tmC, out, 3, dc, sc, bc);
   if (r) return r;
   op->p.M = M; op->p.N = N; op->p.K = K; op->p.G = 1;
   op->p.out = out; op->p.ldc = ldc; op->p.out_group_stride = 0; op->p.out_group_col = 0;

@@ -24,6 +24,7 @@ def _ref(A, W, bias, epi, resid):
     (256, 256, 64, 512, 0), (256, 256, 768, 512, 0), (1000, 2304, 768, 512, 0), (777, 3072, 768, 512, 1),
     (20480, 768, 3072, 512, 0), (9792, 768, 768, 512, 2), (130, 256, 128, 512, 1),
     (20480, 768, 3072, 640, 0), (15616, 768, 768, 640, 0), (300, 128, 64, 640, 1), (777, 384, 768, 640, 2),   # 128-wide pair tiles
+    (1000, 768, 768, 512, 3), (20480, 768, 768, 512, 3), (300, 128, 64, 640, 3),                              # 2-CTA kernel, fp32 out
     (500, 128, 2304, 128, 2), (300, 64, 1152, 64, 2), (260, 32, 576, 32, 2), (20480, 768, 768, 256, 4),
 ])
 def test_gemm(M, N, K, bn, epi):
