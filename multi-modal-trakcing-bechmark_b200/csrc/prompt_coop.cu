@@ -35,7 +35,7 @@ constexpr float kLnEps = 1e-6f;
 constexpr int kCA = 0, kA = 8, kA0 = 72, kCD = 80, kG = 88, kH = 152, kC0 = 160, kSmooth = 161, kFoldFloats = 168;
 constexpr int kSlotBytes = 2 * D * 4 + 2 * D * 2;      // one row pair: two fp32 rows, then two fp16 branch rows
 constexpr int kSmemBytes = 2 * 8 * D * 4 + 3 * D * 4 + kFoldFloats * 4 + kMaxSeq * 32 * 4 + 2 * kThreads * 2 * 4 +
-                           kWarps * kSlotBytes + kWarps * 8 + 64;
+                           kWarps * kSlotBytes + (kWarps + 1) * 8 + 64;
 }  // namespace pc
 
 __device__ __forceinline__ float pc_warp_sum(float v) {
@@ -88,6 +88,7 @@ prompt_coop_kernel(float* __restrict__ x, const op_t* __restrict__ delta, int B,
   float* s_red = s_ms + kMaxSeq * 32;            // [2][kThreads][2] reduction scratch
   uint8_t* s_slots = reinterpret_cast<uint8_t*>(s_red + 2 * kThreads * 2);      // [kWarps][kSlotBytes], 16-byte aligned
   uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_slots + kWarps * kSlotBytes);
+  uint64_t* wbar = s_bar + kWarps;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int lens_x = lens_full - lens_t;
@@ -105,17 +106,24 @@ prompt_coop_kernel(float* __restrict__ x, const op_t* __restrict__ delta, int B,
   // first row pair of phase 1: in flight while the weights are staged
   if (lane == 0 && row_lo + 2 * warp < row_hi)
     pc_prefetch(x, delta, (size_t)(row_lo + 2 * warp), min(2, row_hi - (row_lo + 2 * warp)), slot, bar);
-  for (int i = tid; i < 8 * 192; i += kThreads) {
-    s_wa[i] = reinterpret_cast<const float4*>(wg_a)[i];
-    s_w1[i] = reinterpret_cast<const float4*>(w1t)[i];
+  // weights: five bulk async copies on one CTA-level barrier (no LDG -> STS round trip through registers)
+  if (tid == 0) {
+    mbar_init(wbar, 1);
+    fence_mbar_init();
+    mbar_expect_tx(wbar, 2 * 8 * D * 4 + 3 * D * 4 + kFoldFloats * 4);
+    auto bulk = [&](void* dst, const void* src, uint32_t bytes) {
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                   ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(wbar)) : "memory");
+    };
+    bulk(s_wa, wg_a, 8 * D * 4);
+    bulk(s_w1, w1t, 8 * D * 4);
+    bulk(s_b1, b1, D * 4);
+    bulk(s_g1, gamma1, D * 4);
+    bulk(s_be1, beta1, D * 4);
+    bulk(s_fold, fold, kFoldFloats * 4);
   }
-  if (tid < 192) {
-    s_b1[tid] = reinterpret_cast<const float4*>(b1)[tid];
-    s_g1[tid] = reinterpret_cast<const float4*>(gamma1)[tid];
-    s_be1[tid] = reinterpret_cast<const float4*>(beta1)[tid];
-  }
-  if (tid < kFoldFloats) s_fold[tid] = fold[tid];
-  __syncthreads();
+  __syncthreads();               // barrier initialised before anybody waits on it
+  mbar_wait(wbar, 0);
   const float smooth = s_fold[kSmooth];
 
   // ------------------------------------------------------------------ phase 1: x0 per row
@@ -291,6 +299,7 @@ prompt_coop_kernel(float* __restrict__ x, const op_t* __restrict__ delta, int B,
           s[i] += v[i][j].x + v[i][j].y + v[i][j].z + v[i][j].w;
         }
       }
+      float mean[2], rstd[2];
 #pragma unroll
       for (int i = 0; i < 2; ++i) {
         if (i == 1 && !two) break;
@@ -298,23 +307,26 @@ prompt_coop_kernel(float* __restrict__ x, const op_t* __restrict__ delta, int B,
         float4* xo = reinterpret_cast<float4*>(x + row * D);
 #pragma unroll
         for (int j = 0; j < 6; ++j) xo[lane + 32 * j] = v[i][j];
-        const float mean = pc_warp_sum(s[i]) * (1.0f / D);
+        mean[i] = pc_warp_sum(s[i]) * (1.0f / D);
         float q = 0.f;
 #pragma unroll
         for (int j = 0; j < 6; ++j) {
-          const float a0 = v[i][j].x - mean, a1 = v[i][j].y - mean, a2 = v[i][j].z - mean, a3 = v[i][j].w - mean;
+          const float a0 = v[i][j].x - mean[i], a1 = v[i][j].y - mean[i], a2 = v[i][j].z - mean[i], a3 = v[i][j].w - mean[i];
           q += a0 * a0 + a1 * a1 + a2 * a2 + a3 * a3;
         }
-        const float rstd = rsqrtf(pc_warp_sum(q) * (1.0f / D) + kLnEps);
-        uint2* no = reinterpret_cast<uint2*>(xn + row * D);
+        rstd[i] = rsqrtf(pc_warp_sum(q) * (1.0f / D) + kLnEps);
+      }
 #pragma unroll
-        for (int j = 0; j < 6; ++j) {
-          const float4 g = s_g1[lane + 32 * j];
-          const float4 be = s_be1[lane + 32 * j];
+      for (int j = 0; j < 6; ++j) {              // norm1 scale / shift read once for both rows
+        const float4 g = s_g1[lane + 32 * j];
+        const float4 be = s_be1[lane + 32 * j];
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          if (i == 1 && !two) break;
           uint2 u;
-          u.x = pack_op2((v[i][j].x - mean) * rstd * g.x + be.x, (v[i][j].y - mean) * rstd * g.y + be.y);
-          u.y = pack_op2((v[i][j].z - mean) * rstd * g.z + be.z, (v[i][j].w - mean) * rstd * g.w + be.w);
-          no[lane + 32 * j] = u;
+          u.x = pack_op2((v[i][j].x - mean[i]) * rstd[i] * g.x + be.x, (v[i][j].y - mean[i]) * rstd[i] * g.y + be.y);
+          u.y = pack_op2((v[i][j].z - mean[i]) * rstd[i] * g.z + be.z, (v[i][j].w - mean[i]) * rstd[i] * g.w + be.w);
+          reinterpret_cast<uint2*>(xn + ((size_t)r0 + i) * D)[lane + 32 * j] = u;
         }
       }
     }
