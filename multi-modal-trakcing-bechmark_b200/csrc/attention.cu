@@ -63,6 +63,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tm, op_t* __restrict__ out,
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_trigger();
+  pdl_wait();
   const uint32_t tmem = *tmem_slot;
 
   if (threadIdx.x == 0) {
@@ -222,13 +224,12 @@ int attention_launch(const AttnOp& op, void* out, float* ce_prob, int ce_row, in
   dim3 grid((op.N + kQTile - 1) / kQTile, 12, op.B);
   const float scale_log2 = 0.125f * 1.4426950408889634f;
   const int smem = att_smem_bytes(op.nkp);
-  if (op.nkp <= 256)
-    attention_kernel<256><<<grid, kAttThreads, smem, st>>>(op.tm, reinterpret_cast<op_t*>(out), ce_prob, op.N, op.nkp,
-                                                           ce_row, lens_t, ce_stride, scale_log2);
-  else
-    attention_kernel<512><<<grid, kAttThreads, smem, st>>>(op.tm, reinterpret_cast<op_t*>(out), ce_prob, op.N, op.nkp,
-                                                           ce_row, lens_t, ce_stride, scale_log2);
-  return cudaGetLastError() == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
+  const cudaError_t e =
+      op.nkp <= 256 ? launch_pdl(attention_kernel<256>, grid, kAttThreads, smem, st, op.tm, reinterpret_cast<op_t*>(out), ce_prob,
+                                 op.N, op.nkp, ce_row, lens_t, ce_stride, scale_log2)
+                    : launch_pdl(attention_kernel<512>, grid, kAttThreads, smem, st, op.tm, reinterpret_cast<op_t*>(out), ce_prob,
+                                 op.N, op.nkp, ce_row, lens_t, ce_stride, scale_log2);
+  return e == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
 }
 
 }  // namespace vipt

@@ -134,6 +134,8 @@ attention3_kernel(const __grid_constant__ CUtensorMap tm, op_t* __restrict__ out
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_trigger();
+  pdl_wait();
   const uint32_t tmem = *tmem_slot;
 
   if (warp == 0) {
@@ -473,9 +475,10 @@ int attention3_launch(const AttnOp& op, void* out, float* ce_prob, int ce_row, i
   const int items = op.B * 12;
   const int grid = items < num_sms ? items : num_sms;
   const float scale_log2 = 0.125f * 1.4426950408889634f;
-  attention3_kernel<<<grid, kThreads, smem_bytes(nkp), st>>>(op.tm, reinterpret_cast<op_t*>(out), ce_prob, op.B, op.N, nkp,
-                                                             ch, ce_row, lens_t, ce_stride, scale_log2);
-  return cudaGetLastError() == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
+  return launch_pdl(attention3_kernel, grid, kThreads, smem_bytes(nkp), st, op.tm, reinterpret_cast<op_t*>(out), ce_prob, op.B,
+                    op.N, nkp, ch, ce_row, lens_t, ce_stride, scale_log2) == cudaSuccess
+             ? VIPT_OK
+             : VIPT_ERR_LAUNCH;
 }
 
 }  // namespace vipt

@@ -48,6 +48,8 @@ __global__ void __launch_bounds__(256)
 crop_kernel(const uint8_t* const* __restrict__ frames, const int* __restrict__ frame_hw,
             const double* __restrict__ boxes, double factor, int S, int row_base, int rows_per_seq,
             op_t* __restrict__ apatch, int64_t group_stride, double* __restrict__ geom, int* __restrict__ err) {
+  pdl_trigger();       // programmatic dependent launch protocol (sm100_ptx.cuh); first kernel of a step: its
+  pdl_wait();          // predecessor is the head of the previous step, which wrote the box state read here
   const int b = blockIdx.y;
   const int pix = blockIdx.x * 256 + threadIdx.x;
   const int oy = pix / S, ox = pix % S;
@@ -134,9 +136,9 @@ int launch_crop(const uint8_t* const* frames, const int* frame_hw, const double*
                 int row_base, int rows_per_seq, void* apatch, int64_t group_stride, double* geom, int* err, int B,
                 cudaStream_t st) {
   dim3 grid(S * S / 256, B);
-  crop_kernel<<<grid, 256, 0, st>>>(frames, frame_hw, boxes, factor, S, row_base, rows_per_seq,
+  const cudaError_t e_ = launch_pdl(crop_kernel, grid, 256, 0, st, frames, frame_hw, boxes, factor, S, row_base, rows_per_seq,
                                     reinterpret_cast<op_t*>(apatch), group_stride, geom, err);
-  return cudaGetLastError() == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
+  return e_ == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
 }
 
 int launch_patchify(const float* img, int S, int row_base, int rows_per_seq, void* apatch, int64_t group_stride, int B,

@@ -6,6 +6,7 @@
 
 #include <math.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <cuda_fp16.h>
@@ -25,6 +26,19 @@ namespace vipt {
     int r_ = (x);       \
     if (r_) return r_;  \
   } while (0)
+
+// Programmatic dependent launch (sm100_ptx.cuh) is switched per engine before it enqueues or captures a step.
+// Latency mode (few sequences: every kernel is short, launch gaps and prologues are a visible part of a step):
+// on, batch-1 p50 0.920 -> 0.857 ms.  Throughput mode (64 sequences): the step is power-capped, PDL changes
+// nothing on the device (4.151 ms with and without) and the resident-but-waiting CTAs of the next kernels delay
+// the concurrent host-frame gather kernel of the pipelined API (e2e 4.25 -> 4.71 ms), so it is off.
+// VIPT_PDL=0|1 forces it.
+static thread_local bool g_pdl_on = false;
+bool pdl_enabled() { return g_pdl_on; }
+void pdl_select(int batch, int num_sms) {
+  static const char* force = getenv("VIPT_PDL");
+  g_pdl_on = force ? force[0] == '1' : batch * 12 < num_sms;
+}
 
 Engine::~Engine() {
   if (graph_exec) cudaGraphExecDestroy(graph_exec);

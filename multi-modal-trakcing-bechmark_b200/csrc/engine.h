@@ -130,4 +130,6 @@ struct Engine {
   int track_enqueue(const void* frame_ptrs_dev, bool use_graph, cudaStream_t st);
 };
 
+void pdl_select(int batch, int num_sms);     // engine.cu: programmatic dependent launch on/off for the next launches
+
 }  // namespace vipt

@@ -128,6 +128,7 @@ int Engine::finalize_buffers() {
 int Engine::run_backbone_head(bool tracking, bool want_feat32, int debug_stop, cudaStream_t st) {
   long nl = 0;
   int stage = 0;
+  pdl_select(B, num_sms);
   static const bool use_cluster_prompt = getenv("VIPT_PROMPT_CLUSTER") != nullptr;
 #define LAUNCH(cls, expr)   \
   do {                      \
@@ -258,6 +259,7 @@ int Engine::track_enqueue(const void* frame_ptrs_dev, bool use_graph, cudaStream
   const int64_t gs = (int64_t)B * kLensFull * 768;
   auto body = [&](cudaStream_t s) -> int {
     // search: factor 4.0 -> 256 x 256 around the current state (vipt.py:67-69)
+    pdl_select(B, num_sms);
     prof_begin(K_CROP, s);
     RET(launch_crop(frame_ptrs, frame_hw, state, 4.0, 256, kLensT, kLensFull, apatch, gs, geom_x, err, B, s));
     prof_end(s);

@@ -79,6 +79,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_trigger();                   // programmatic dependent launch protocol, see sm100_ptx.cuh
+  pdl_wait();
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
@@ -279,8 +281,8 @@ static int launch_t(const GemmOp& op, int num_sms, cudaStream_t st) {
   }
   const int tiles = op.p.G * ((op.p.M + BM - 1) / BM) * (op.p.N / BN);
   const int grid = tiles < num_sms ? tiles : num_sms;
-  gemm_kernel<BN, EPI><<<grid, kThreads, Cfg::kSmemBytes, st>>>(op.tmA, op.tmB, op.p);
-  return cudaGetLastError() == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
+  return launch_pdl(gemm_kernel<BN, EPI>, grid, kThreads, Cfg::kSmemBytes, st, op.tmA, op.tmB, op.p) == cudaSuccess ? VIPT_OK
+                                                                                                          : VIPT_ERR_LAUNCH;
 }
 
 template <int BN>

@@ -140,6 +140,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   __syncthreads();
   cluster_sync_all();              // peer barriers are initialised before any remote arrive / multicast
   tc_fence_after();
+  pdl_trigger();                   // programmatic dependent launch protocol, see sm100_ptx.cuh
+  pdl_wait();
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
@@ -309,8 +311,9 @@ static int launch2_t(const GemmOp& op, int num_sms, cudaStream_t st) {
   int grid = 2 * tiles;
   const int cap = num_sms & ~1;
   if (grid > cap) grid = cap;
-  gemm2_kernel<EPI, BN><<<grid, g2::kThreads, g2::Cfg<BN>::kSmemBytes, st>>>(op.tmA, op.tmB, op.tmC, op.p);
-  return cudaGetLastError() == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
+  return launch_pdl(gemm2_kernel<EPI, BN>, grid, g2::kThreads, g2::Cfg<BN>::kSmemBytes, st, op.tmA, op.tmB, op.tmC, op.p) == cudaSuccess
+             ? VIPT_OK
+             : VIPT_ERR_LAUNCH;
 }
 
 int gemm2_launch(const GemmOp& op, int num_sms, cudaStream_t st) {

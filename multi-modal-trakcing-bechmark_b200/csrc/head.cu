@@ -40,6 +40,8 @@ head_final_kernel(const op_t* __restrict__ h4, const float* __restrict__ w5, con
                   const double* __restrict__ geom, const int* __restrict__ frame_hw, double* __restrict__ out_boxes,
                   float* __restrict__ out_scores) {
   __shared__ float s_w5[5 * 32 + 5];
+  pdl_trigger();       // programmatic dependent launch protocol (sm100_ptx.cuh)
+  pdl_wait();
   __shared__ float s_v[8];
   __shared__ int s_i[8];
   __shared__ float s_size[2][256], s_off[2][256];
@@ -111,9 +113,8 @@ head_final_kernel(const op_t* __restrict__ h4, const float* __restrict__ w5, con
 int launch_head_final(const void* h4, const float* w5, const float* b5, const float* window, float* score_map,
                       float* size_map, float* offset_map, float* pred_boxes, double* state, const double* geom,
                       const int* frame_hw, double* out_boxes, float* out_scores, int B, cudaStream_t st) {
-  head_final_kernel<<<B, 256, 0, st>>>(reinterpret_cast<const op_t*>(h4), w5, b5, window, score_map, size_map,
-                                       offset_map, pred_boxes, state, geom, frame_hw, out_boxes, out_scores);
-  return cudaGetLastError() == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
+  const cudaError_t e_ = launch_pdl(head_final_kernel, B, 256, 0, st, reinterpret_cast<const op_t*>(h4), w5, b5, window, score_map, size_map, offset_map, pred_boxes, state, geom, frame_hw, out_boxes, out_scores);
+  return e_ == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
 }
 
 }  // namespace vipt

@@ -123,6 +123,8 @@ prompt_coop_kernel(float* __restrict__ x, const op_t* __restrict__ delta, int B,
     bulk(s_fold, fold, kFoldFloats * 4);
   }
   __syncthreads();               // barrier initialised before anybody waits on it
+  pdl_trigger();                 // the next kernel's CTAs may start their prologue (sm100_ptx.cuh); this kernel itself is a
+                                 // cooperative launch without the programmatic attribute, so it has nothing to wait for
   mbar_wait(wbar, 0);
   const float smooth = s_fold[kSmooth];
 

@@ -220,4 +220,36 @@ __device__ __forceinline__ void gelu_erf2x2(float& x0, float& x1) {
   asm("mov.b64 {%0, %1}, %2;" : "=f"(x0), "=f"(x1) : "l"(r));
 }
 
+// ---- programmatic dependent launch (PDL) -------------------------------------------------------------------
+// In latency mode (engine.cu: pdl_select) every kernel of a tracking step is launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization (launch_pdl below), so inside the CUDA graph consecutive
+// kernels are joined by programmatic edges: the CTAs
+// of kernel n+1 become resident and run their prologue (barrier init, TMEM allocation, descriptor prefetch,
+// weight staging) while kernel n drains its last tiles, and only then block in pdl_wait() until kernel n has
+// completed and its writes are visible.  Protocol, identical in every kernel:
+//   prologue that touches no global memory written by another kernel   (kernel parameters and weights are fine)
+//   pdl_trigger();   // AFTER the prologue: a successor's CTA can only appear once every CTA of this grid owns its
+//                    // shared memory and TMEM, so a successor can never take a resource this grid still needs
+//   pdl_wait();      // all threads; before the first read of upstream data and before the first global write
+// Both instructions are no-ops when the grid was launched without the attribute.
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+bool pdl_enabled();      // engine.cu: set per engine by pdl_select()
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 }  // namespace vipt

@@ -80,6 +80,8 @@ __global__ void __launch_bounds__(256)
 ln_rows_kernel(const float* x_in, int n_in, const op_t* __restrict__ delta, const int* __restrict__ perm, int perm_stride,
                float* x_out, op_t* __restrict__ xn, const float* __restrict__ gamma,
                const float* __restrict__ beta, int B, int n_out, int lens_t) {
+  pdl_trigger();       // programmatic dependent launch protocol (sm100_ptx.cuh)
+  pdl_wait();
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
   if (row >= B * n_out) return;
@@ -101,10 +103,10 @@ ln_rows_kernel(const float* x_in, int n_in, const op_t* __restrict__ delta, cons
 int launch_ln_rows(const float* x_in, int n_in, const void* delta, const int* perm, int perm_stride, float* x_out, void* xn,
                    const float* gamma, const float* beta, int B, int n_out, int lens_t, cudaStream_t st) {
   const int rows = B * n_out;
-  ln_rows_kernel<<<(rows + 7) / 8, 256, 0, st>>>(x_in, n_in, reinterpret_cast<const op_t*>(delta), perm, perm_stride, x_out,
-                                                 reinterpret_cast<op_t*>(xn),
-                                                 gamma, beta, B, n_out, lens_t);
-  return cudaGetLastError() == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
+  return launch_pdl(ln_rows_kernel, (rows + 7) / 8, 256, 0, st, x_in, n_in, reinterpret_cast<const op_t*>(delta), perm, perm_stride,
+                    x_out, reinterpret_cast<op_t*>(xn), gamma, beta, B, n_out, lens_t) == cudaSuccess
+             ? VIPT_OK
+             : VIPT_ERR_LAUNCH;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -134,7 +136,9 @@ prompt_a_kernel(const float* __restrict__ xa, const op_t* __restrict__ delta, in
   for (int i = threadIdx.x; i < 2 * 8 * 192; i += 256)
     ws4[i] = (i < 8 * 192) ? reinterpret_cast<const float4*>(w.wg_a)[i]
                            : reinterpret_cast<const float4*>(w.wg_d)[i - 8 * 192];
-  __syncthreads();
+  __syncthreads();     // weights are static: staged before the upstream kernel has finished
+  pdl_trigger();       // programmatic dependent launch protocol (sm100_ptx.cuh)
+  pdl_wait();
   const int lane = threadIdx.x & 31;
   const int groups_per_b = lens_full / kTok;
   const int n_tasks = B * groups_per_b * 2;          // task = (4 consecutive positions, stream)
@@ -231,9 +235,8 @@ int launch_prompt_a(const float* xa, const void* delta, int n_cur, const int* sl
   const int tasks = B * (lens_full / kTok) * 2;
   int grid = (tasks + 7) / 8;
   if (grid > 148 * 2) grid = 148 * 2;      // persistent: the 48 KB weight tile is staged once per CTA
-  prompt_a_kernel<<<grid, 256, smem, st>>>(xa, reinterpret_cast<const op_t*>(delta), n_cur, slot_of_pos, xd_src, w, xd, B, lens_t,
-                                           lens_full);
-  return cudaGetLastError() == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
+  const cudaError_t e_ = launch_pdl(prompt_a_kernel, grid, 256, smem, st, xa, reinterpret_cast<const op_t*>(delta), n_cur, slot_of_pos, xd_src, w, xd, B, lens_t, lens_full);
+  return e_ == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
 }
 
 }  // namespace vipt

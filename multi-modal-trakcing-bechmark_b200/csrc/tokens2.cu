@@ -24,6 +24,8 @@ __device__ __forceinline__ float warp_sum2(float v) {
 __global__ void __launch_bounds__(256)
 fovea_kernel(const float* __restrict__ xd, float smooth, float* __restrict__ F, int lens_t, int lens_full) {
   __shared__ float s_red[8][8];
+  pdl_trigger();       // programmatic dependent launch protocol (sm100_ptx.cuh)
+  pdl_wait();
   const int b = blockIdx.x, dom = blockIdx.y, t = threadIdx.x;
   const int dom0 = dom == 0 ? 0 : lens_t;
   const int domL = dom == 0 ? lens_t : lens_full - lens_t;
@@ -78,8 +80,8 @@ fovea_kernel(const float* __restrict__ xd, float smooth, float* __restrict__ F, 
 
 int launch_fovea(const float* xd, float smooth, float* F, int B, int lens_t, int lens_full, cudaStream_t st) {
   if (lens_t > 256 || lens_full - lens_t > 256) return VIPT_ERR_ARG;
-  fovea_kernel<<<dim3(B, 2), 256, 0, st>>>(xd, smooth, F, lens_t, lens_full);
-  return cudaGetLastError() == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
+  const cudaError_t e_ = launch_pdl(fovea_kernel, dim3(B, 2), 256, 0, st, xd, smooth, F, lens_t, lens_full);
+  return e_ == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
 }
 
 // Prompt phase B.  grid: B * (lens_full / 8); tile = 8 consecutive full-grid positions.
@@ -96,6 +98,8 @@ prompt_b_kernel(const float* __restrict__ F, const float* __restrict__ w1, const
                 int lens_full) {
   __shared__ float s_f[kTileTok][8];
   __shared__ float s_part[kTileTok][6][2];
+  pdl_trigger();       // programmatic dependent launch protocol (sm100_ptx.cuh)
+  pdl_wait();
   __shared__ int s_row[kTileTok];
   const int tid = threadIdx.x;
   const int tiles_per_b = lens_full / kTileTok;
@@ -196,11 +200,8 @@ prompt_b_kernel(const float* __restrict__ F, const float* __restrict__ w1, const
 int launch_prompt_b(const float* F, const float* w1, const float* b1, float* P, const float* base, const void* delta,
                     float* x, int n_cur, const int* slot_of_pos, const float* pos_embed, const float* gamma1,
                     const float* beta1, void* xn, int B, int lens_t, int lens_full, cudaStream_t st) {
-  prompt_b_kernel<<<B * (lens_full / kTileTok), kBThreads, 0, st>>>(F, w1, b1, P, base, reinterpret_cast<const op_t*>(delta), x, n_cur,
-                                                                     slot_of_pos,
-                                                                     pos_embed, gamma1, beta1,
-                                                                     reinterpret_cast<op_t*>(xn), lens_t, lens_full);
-  return cudaGetLastError() == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
+  const cudaError_t e_ = launch_pdl(prompt_b_kernel, B * (lens_full / kTileTok), kBThreads, 0, st, F, w1, b1, P, base, reinterpret_cast<const op_t*>(delta), x, n_cur, slot_of_pos, pos_embed, gamma1, beta1, reinterpret_cast<op_t*>(xn), lens_t, lens_full);
+  return e_ == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -216,6 +217,8 @@ ce_topk_kernel(const float* __restrict__ ce_prob, int n_heads, int n_s, int n_ke
                int* __restrict__ gi_out, int* __restrict__ perm, int* __restrict__ removed,
                int* __restrict__ slot_of_pos, float* __restrict__ score_out, int lens_x) {
   __shared__ float s_score[256];
+  pdl_trigger();       // programmatic dependent launch protocol (sm100_ptx.cuh)
+  pdl_wait();
   const int b = blockIdx.x, j = threadIdx.x;
   float sc = -INFINITY;
   if (j < n_s) {
@@ -246,9 +249,8 @@ ce_topk_kernel(const float* __restrict__ ce_prob, int n_heads, int n_s, int n_ke
 int launch_ce_topk(const float* ce_prob, int n_heads, int n_s, int n_keep, const int* gi_in, int* gi_out, int* perm,
                    int* removed, int* slot_of_pos, float* score_out, int lens_x, int B, cudaStream_t st) {
   if (n_s > 256) return VIPT_ERR_ARG;
-  ce_topk_kernel<<<B, 256, 0, st>>>(ce_prob, n_heads, n_s, n_keep, gi_in, gi_out, perm, removed, slot_of_pos, score_out,
-                                    lens_x);
-  return cudaGetLastError() == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
+  const cudaError_t e_ = launch_pdl(ce_topk_kernel, B, 256, 0, st, ce_prob, n_heads, n_s, n_keep, gi_in, gi_out, perm, removed, slot_of_pos, score_out, lens_x);
+  return e_ == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -261,6 +263,8 @@ final_norm_kernel(const float* __restrict__ x, const op_t* __restrict__ delta, i
                   const int* __restrict__ slot_of_pos,
                   const float* __restrict__ gamma, const float* __restrict__ beta, op_t* __restrict__ feat16,
                   float* __restrict__ feat32, int B, int lens_t, int lens_full) {
+  pdl_trigger();       // programmatic dependent launch protocol (sm100_ptx.cuh)
+  pdl_wait();
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
   if (row >= B * lens_full) return;
@@ -323,10 +327,8 @@ final_norm_kernel(const float* __restrict__ x, const op_t* __restrict__ delta, i
 int launch_final_norm(const float* x, const void* delta, int n_cur, const int* slot_of_pos, const float* gamma, const float* beta,
                       void* feat16, float* feat32, int B, int lens_t, int lens_full, cudaStream_t st) {
   const int rows = B * lens_full;
-  final_norm_kernel<<<(rows + 7) / 8, 256, 0, st>>>(x, reinterpret_cast<const op_t*>(delta), n_cur, slot_of_pos, gamma, beta,
-                                                    reinterpret_cast<op_t*>(feat16),
-                                                    feat32, B, lens_t, lens_full);
-  return cudaGetLastError() == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
+  const cudaError_t e_ = launch_pdl(final_norm_kernel, (rows + 7) / 8, 256, 0, st, x, reinterpret_cast<const op_t*>(delta), n_cur, slot_of_pos, gamma, beta, reinterpret_cast<op_t*>(feat16), feat32, B, lens_t, lens_full);
+  return e_ == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
 }
 
 }  // namespace vipt

