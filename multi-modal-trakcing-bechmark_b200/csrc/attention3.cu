@@ -1,8 +1,8 @@
 // Persistent, warp-specialised joint template+search attention (ViPT/lib/models/layers/attn.py:33-59) for
 // N > 128 tokens, third generation: the score MMAs run AHEAD of the softmax instead of in lock-step with it.
 //
-// One CTA per SM loops over (sequence, head) items; K and V of an item are loaded once and reused by all
-// its 128-query tiles.  The keys of a tile are cut into <= 3 chunks of <= 128 keys.  Chunks of all tiles and
+// One CTA per SM walks a contiguous range of (sequence, head, 128-query tile) units; K and V of a (sequence, head)
+// item are loaded once per CTA that touches it and reused by its tiles.  The keys of a tile are cut into <= 3 chunks of <= 128 keys.  Chunks of all tiles and
 // items form one stream k = 0, 1, 2, ...:
 //
 //   warp 0        TMA producer   Q tiles (double-buffered), K (double-buffered, next item prefetched), V
@@ -116,10 +116,17 @@ attention3_kernel(const __grid_constant__ CUtensorMap tm, op_t* __restrict__ out
   const int cb1 = ch.base[1], cb2 = ch.base[2], cw0 = ch.w[0], cw1 = ch.w[1], cw2 = ch.w[2];
   auto chunk_base = [&](int j) { return j == 0 ? 0 : (j == 1 ? cb1 : cb2); };
   auto chunk_w = [&](int j) { return j == 0 ? cw0 : (j == 1 ? cw1 : cw2); };
-  const int n_items = B * 12;
-  const int n_local = (int)blockIdx.x < n_items ? (n_items - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+  // Work is cut at (item, query tile) granularity: CTA c owns the contiguous unit range [u0, u1) of the item-major list of
+  // B * 12 * T units (64 sequences at N = 320: 2304 units over 148 CTAs = 15.6, so every CTA gets 15 or 16 tiles; with whole
+  // items it was 768 / 148 = 5.2, i.e. 18 tiles on some CTAs and 15 on the others).  A CTA whose range starts or ends inside
+  // an item loads that item's K / V like any other and simply runs fewer of its tiles.
+  const int n_units = B * 12 * T;
+  const int u0 = (int)(((long long)blockIdx.x * n_units) / (int)gridDim.x);
+  const int u1 = (int)(((long long)(blockIdx.x + 1) * n_units) / (int)gridDim.x);
+  const int item0 = u0 / T, t0 = u0 - item0 * T;      // first item of this CTA and the tile it starts at
+  const int n_local = u1 > u0 ? (u1 - 1) / T - item0 + 1 : 0;      // items touched
   const int per_item = T * NC;
-  const int total = n_local * per_item;
+  const int total = (u1 - u0) * NC;                   // chunks in this CTA's stream
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tm);
@@ -139,30 +146,33 @@ attention3_kernel(const __grid_constant__ CUtensorMap tm, op_t* __restrict__ out
   const uint32_t tmem = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0 && n_local > 0) {
+    if (lane == 0 && total > 0) {
       // ------------------------------------------------------------ TMA producer
       int g = 0;
       for (int n = 0; n < n_local; ++n) {
-        const int item = blockIdx.x + n * gridDim.x;
+        const int item = item0 + n;
         const int b = item / 12, h = item % 12;
+        const int ts = n == 0 ? t0 : 0;                  // tiles [ts, te) of this item belong to this CTA
+        const int te = min(T, u1 - item * T);
+        const int tv = te - ts > 1 ? ts + 1 : ts;        // V is requested after the second Q tile (needed later than both)
         if (n == 0) {
           mbar_expect_tx(&bars[K_FULL], kbytes);
           for (int i = 0; i < nbox; ++i) tma_load_3d(sK + i * kBoxBytes, &tm, &bars[K_FULL], 768 + h * kHd, i * 64, b);
         }
-        for (int t = 0; t < T; ++t, ++g) {
+        for (int t = ts; t < te; ++t, ++g) {
           const int qb = g & 1;
           mbar_wait(&bars[Q_EMPTY + qb], ((g >> 1) & 1) ^ 1);
           mbar_expect_tx(&bars[Q_FULL + qb], 2 * kBoxBytes);
           tma_load_3d(sQ + qb * kQBytes, &tm, &bars[Q_FULL + qb], h * kHd, t * kQTile, b);
           tma_load_3d(sQ + qb * kQBytes + kBoxBytes, &tm, &bars[Q_FULL + qb], h * kHd, t * kQTile + 64, b);
-          if (t == 0 && n + 1 < n_local) {       // prefetch the next item's K into the other buffer
-            const int nxt = item + gridDim.x, kb = (n + 1) & 1;
+          if (t == ts && n + 1 < n_local) {      // prefetch the next item's K into the other buffer
+            const int nxt = item + 1, kb = (n + 1) & 1;
             mbar_wait(&bars[K_EMPTY + kb], (((n + 1) >> 1) & 1) ^ 1);
             mbar_expect_tx(&bars[K_FULL + kb], kbytes);
             for (int i = 0; i < nbox; ++i)
               tma_load_3d(sK + kb * kbytes + i * kBoxBytes, &tm, &bars[K_FULL + kb], 768 + (nxt % 12) * kHd, i * 64, nxt / 12);
           }
-          if (t == (T > 1 ? 1 : 0)) {            // after the second Q tile: V is needed later than both
+          if (t == tv) {
             mbar_wait(&bars[V_EMPTY], (n & 1) ^ 1);
             mbar_expect_tx(&bars[V_FULL], kbytes);
             for (int i = 0; i < nbox; ++i) tma_load_3d(sV + i * kBoxBytes, &tm, &bars[V_FULL], 1536 + h * kHd, i * 64, b);
@@ -179,11 +189,11 @@ attention3_kernel(const __grid_constant__ CUtensorMap tm, op_t* __restrict__ out
       const uint64_t d0 = make_sdesc_sw128(smem_u32(sQ));
       const uint32_t hi = (uint32_t)(d0 >> 32), q_lo = (uint32_t)d0;
       const uint32_t k_lo = (uint32_t)make_sdesc_sw128(smem_u32(sK));
-      Pos ps = {0, 0, 0, 0};
+      Pos ps = {0, t0, 0, 0};
       for (int ks = 0; ks < total; ++ks) {
         const int sb = ks % 3;
         if (ps.j == 0) {
-          if (ps.t == 0) mbar_wait(&bars[K_FULL + (ps.n & 1)], (ps.n >> 1) & 1);
+          if (ps.t == 0 || ks == 0) mbar_wait(&bars[K_FULL + (ps.n & 1)], (ps.n >> 1) & 1);
           mbar_wait(&bars[Q_FULL + (ps.g & 1)], (ps.g >> 1) & 1);
         }
         if (ks >= 3) mbar_wait(&bars[S_EMPTY + sb], ((ks / 3) & 1) ^ 1);
@@ -213,10 +223,10 @@ attention3_kernel(const __grid_constant__ CUtensorMap tm, op_t* __restrict__ out
       const uint64_t d0 = make_sdesc_sw128(smem_u32(sP));
       const uint32_t hi = (uint32_t)(d0 >> 32), p_lo = (uint32_t)d0;
       const uint32_t v_lo = (uint32_t)make_sdesc_sw128(smem_u32(sV));
-      Pos pp = {0, 0, 0, 0};
+      Pos pp = {0, t0, 0, 0};
       for (int kp = 0; kp < total; ++kp) {
         const int ob = kp & 1;
-        if (pp.j == 0 && pp.t == 0) mbar_wait(&bars[V_FULL], pp.n & 1);
+        if (pp.j == 0 && (pp.t == 0 || kp == 0)) mbar_wait(&bars[V_FULL], pp.n & 1);
         if (kp >= 2) mbar_wait(&bars[O_EMPTY + ob], ((kp >> 1) & 1) ^ 1);
         mbar_wait(&bars[P_FULL + ob], (kp >> 1) & 1);
         tc_fence_after();
@@ -246,7 +256,8 @@ attention3_kernel(const __grid_constant__ CUtensorMap tm, op_t* __restrict__ out
     const uint32_t t_lane = tmem + ((uint32_t)(wr * 32) << 16);
     const uint32_t pbuf = smem_u32(sP + grp * kPBytes) + row * 128;      // 32-bit shared address: STS, not generic ST
     for (int k = grp; k < total; k += 2) {
-      const int n = k / per_item, r = k - n * per_item;
+      const int kk = k + t0 * NC;                 // position in the item-aligned chunk stream
+      const int n = kk / per_item, r = kk - n * per_item;
       const int t = r / NC, j = r - t * NC;
       const int q0 = t * kQTile;
       const int base = chunk_base(j);
@@ -355,11 +366,11 @@ attention3_kernel(const __grid_constant__ CUtensorMap tm, op_t* __restrict__ out
     const uint32_t t_lane = tmem + ((uint32_t)(wr * 32) << 16);
     float acc[kHd];
     float m_run = 0.f, l_run = 0.f;
-    Pos p = {0, 0, 0, 0};
+    Pos p = {0, t0, 0, 0};
     for (int k = 0; k < total; ++k) {
       const int ob = k & 1;
       const int q0 = p.t * kQTile;
-      const int item = blockIdx.x + p.n * gridDim.x;
+      const int item = item0 + p.n;
       const int b = item / 12, h = item % 12;
       mbar_wait(&bars[ST_FULL + (k & 3)], (k >> 2) & 1);
       mbar_wait(&bars[O_FULL + ob], (k >> 1) & 1);

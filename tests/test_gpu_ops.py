@@ -71,7 +71,8 @@ def test_crop_too_small_box_sets_error():
 
 
 @pytest.mark.parametrize("B,N", [(2, 320), (3, 244), (2, 190), (5, 153), (1, 64),
-                                 (13, 320), (14, 244), (13, 190), (15, 153)])   # B * 12 >= #SMs: persistent kernel
+                                 (13, 320), (14, 244), (13, 190), (15, 153),    # B * 12 >= #SMs: persistent kernel,
+                                 (64, 320), (64, 153)])                         # work split inside (sequence, head) items
 def test_attention(B, N):
     L = _lib.lib()
     g = torch.Generator(device="cuda").manual_seed(N)
