@@ -145,35 +145,41 @@ def test_host_roi_upload_matches_device_frames(pinned):
         np.testing.assert_array_equal(a.engine.results()[0], b2)
 
 
-def test_full_size_batch64_against_oracle():
-    """BASELINE.json configs[1] at full size: 64 concurrent LasHeR-shaped RGBT sequences in one engine (the 2-CTA
-    GEMM, persistent attention and cooperative prompt kernels are selected only at this scale), CUDA-graph replay.
+@pytest.mark.parametrize("ptype,modality,B,checked", [
+    ("vipt_deep", "rgbt", 64, (0, 1, 4)),       # BASELINE.json configs[1]: 64 LasHeR-shaped sequences per B200
+    ("vipt_deep", "rgbe", 64, (2,)),            # configs[2]: VisEvent-shaped, the per-GPU shard of the 2/4/8-GPU runs
+    ("vipt_shaw", "rgbd", 32, (12, 14, 15)),    # configs[3]: shallow prompt, 256 sequences over 8 GPUs = 32 per GPU
+])
+def test_full_size_batch_against_oracle(ptype, modality, B, checked):
+    """BASELINE.json configs at full per-GPU size: B concurrent sequences in one engine (the 2-CTA GEMM, persistent
+    attention and cooperative prompt kernels are selected only at this scale), CUDA-graph replay.
     (i) slots carrying the same sequence give bit-identical boxes and scores (no cross-slot leakage, deterministic);
-    (ii) three slots are checked against the CPU oracle on the first tracked frame (both sides start from the init box):
-         boxes within 0.5 px and score maps within 1e-2 of the map maximum unless the fp32 reference is at a near-tie."""
-    B, T, ND = 64, 3, 16
-    ptype = "vipt_deep"
+    (ii) slots are checked against the CPU oracle on the first tracked frame (both sides start from the init box):
+         boxes within 0.5 px and score maps within 1e-2 of the map maximum unless the fp32 reference is at a near-tie.
+    `checked` = the sequences of this seed range at which the fp32 reference is NOT at a documented near-tie on
+    frame 1 (synthetic weights give flat CE scores: most sequences are)."""
+    T, ND = 3, 16
     sd = synth.synthetic_state_dict(ptype, 0)
-    base = [synth.synthetic_sequence(300 + i, T, "rgbt") for i in range(ND)]
+    base = [synth.synthetic_sequence(300 + i, T, modality) for i in range(ND)]
     trk = BatchedViPTTracker(sd, B, ptype, use_graph=True)
     trk.initialize([base[i % ND][0][0] for i in range(B)], [base[i % ND][1] for i in range(B)])
     boxes1, scores1 = trk.track([base[i % ND][0][1] for i in range(B)])
     boxes1, scores1 = boxes1.copy(), scores1.copy()
     sm1 = trk.engine.buffer("score_map").cpu().view(B, -1).clone()
     agree = 0
-    for i in (0, 1, 4):      # sequences at which the fp32 reference is NOT at a near-tie on frame 1 (12 of these 16 are)
+    for i in checked:
         ref = vo.OracleTracker(sd, ptype)
         ref.initialize(base[i][0][0], {"init_bbox": list(base[i][1])})
         r = ref.track(base[i][0][1])
         ref_sm = ref.last["out"]["score_map"].view(-1)
         tie = bool(near_tie.is_near_tie(ref.last["out"], ref.window)[0])
-        for slot in (i, i + 48):
+        for slot in (i, i + B - ND):
             d = float(np.abs(boxes1[slot] - np.asarray(r["target_bbox"])).max())
             e = float((sm1[slot] - ref_sm).abs().max() / ref_sm.max())
             ok = d < 0.5 and e < 1e-2 and abs(scores1[slot] - r["best_score"]) < 1e-2 * r["best_score"]
             agree += ok
             assert ok or tie, "slot %d: box %.3f px, score map %.2e, reference not at a near-tie" % (slot, d, e)
-    assert agree >= 4, agree
+    assert 3 * agree >= 2 * 2 * len(checked), agree
     for t in range(1, T):
         if t > 1:
             boxes, scores = trk.track([base[i % ND][0][t] for i in range(B)])
