@@ -99,7 +99,21 @@ int Engine::finalize_buffers() {
     if (pair_tiles >= num_sms / 2) return gemm2_plan(op, A, lda, W, K, M, N, K, epi, out, N, bias, num_sms / 2);
     const int mt = (M + 127) / 128;
     int bn = 128;
-    while (bn > 32 && mt * (N / bn) < num_sms) bn >>= 1;
+    static const bool old_policy = getenv("VIPT_BN_POLICY_OLD") != nullptr;
+    if (old_policy) {
+      while (bn > 32 && mt * (N / bn) < num_sms) bn >>= 1;
+    } else {
+      // These GEMMs are bound by the operand stream into each SM ((128 + bn) x 64 fp16 per k-block), not by the MMAs:
+      // pick the tile width that minimises  rounds x (128 + bn), ties to the wider tile (less total L2 traffic).
+      // E.g. one sequence (3 row tiles): qkv 108 x bn64 tiles in one round instead of 216 x bn32 in two.  Measured
+      // against the previous rule (narrowest tile that still gives >= #SMs tiles): step 0.848 -> 0.828 ms at one
+      // sequence, 1.058 -> 0.979 at 4, 1.297 -> 1.181 at 8, 1.628 -> 1.574 at 16 (VIPT_BN_POLICY_OLD=1 restores it).
+      int best = 1 << 30;
+      for (int c = 128; c >= 32; c >>= 1) {
+        const int tiles = mt * (N / c), rounds = (tiles + num_sms - 1) / num_sms, cost = rounds * (128 + c);
+        if (cost < best) { best = cost; bn = c; }
+      }
+    }
     return gemm_plan(op, A, lda, 0, W, K, 0, 1, M, N, K, bn, epi, out, N, 0, 0, bias, nullptr);
   };
   for (int i = 0; i < kDepth; ++i) {

@@ -14,7 +14,8 @@ sd = synth.synthetic_state_dict("vipt_deep", 0)
 base = [synth.synthetic_sequence(1000 + s, RING + 1, "rgbt") for s in range(ND)]
 rows = []
 ref_box = None
-for B in (1, 2, 4, 8, 16, 32, 64, 96, 128):
+BS = [int(b) for b in sys.argv[3].split(",")] if len(sys.argv) > 3 else [1, 2, 4, 8, 16, 32, 64, 96, 128]
+for B in BS:
     trk = BatchedViPTTracker(sd, B, "vipt_deep", use_graph=True)
     eng = trk.engine
     dev = eng.device
