@@ -129,9 +129,21 @@ int Engine::finalize_buffers() {
   const int MH = B * kLensX;
   // center head: implicit 3x3 convolutions (no im2col buffer); BN folded, ReLU fused, towers grouped
   if (B * 3 >= num_sms / 2) RET(gemm2_plan_conv(&g_c1, feat16, 768, 768, w_c1, B, 768, EPI_RELU_F16, h1, 768, b_c1));
-  else RET(gemm_plan_conv(&g_c1, feat16, 768, 768, 0, w_c1, 1, B, 768, 64, EPI_RELU_F16, h1, 768, 0, b_c1));
-  RET(gemm_plan_conv(&g_c2, h1, 768, 256, 256, w_c2, 3, B, 128, 128, EPI_RELU_F16, h2, 384, 128, b_c2));
-  RET(gemm_plan_conv(&g_c3, h2, 384, 128, 128, w_c3, 3, B, 64, 64, EPI_RELU_F16, h3, 192, 64, b_c3));
+  // latency mode: same operand-stream rule as the linear layers (the towers have only 2 row tiles per sequence and
+  // K = 9 x C_in, so narrow tiles put them on more SMs and shorten each CTA's stream).  A split of K with a fix-up
+  // through L2 (partial tiles, counter, last CTA reduces) was measured and lost: 0.828 -> 1.017 ms at one sequence.
+  auto pick_bn = [&](int row_tiles, int N, int max_bn) {
+    int bn = max_bn, best = 1 << 30;
+    for (int c = max_bn; c >= 32; c >>= 1) {
+      const int tiles = row_tiles * (N / c), rounds = (tiles + num_sms - 1) / num_sms, cost = rounds * (128 + c);
+      if (cost < best) { best = cost; bn = c; }
+    }
+    return bn;
+  };
+  const bool lat = B * 3 < num_sms / 2;
+  if (lat) RET(gemm_plan_conv(&g_c1, feat16, 768, 768, 0, w_c1, 1, B, 768, pick_bn(2 * B, 768, 64), EPI_RELU_F16, h1, 768, 0, b_c1));
+  RET(gemm_plan_conv(&g_c2, h1, 768, 256, 256, w_c2, 3, B, 128, lat ? pick_bn(6 * B, 128, 128) : 128, EPI_RELU_F16, h2, 384, 128, b_c2));
+  RET(gemm_plan_conv(&g_c3, h2, 384, 128, 128, w_c3, 3, B, 64, lat ? pick_bn(6 * B, 64, 64) : 64, EPI_RELU_F16, h3, 192, 64, b_c3));
   RET(gemm_plan_conv(&g_c4, h3, 192, 64, 64, w_c4, 3, B, 32, 32, EPI_RELU_F16, h4, 96, 32, b_c4));
   finalized = true;
   return VIPT_OK;
