@@ -259,6 +259,14 @@ def run_ours(args):
                      "how": "CUDA-event pair around every launch of one un-graphed step (mean of %d steps)" % nprof,
                      "whole_step_tflops": GF_TOTAL * 1e9 * B / (ms / K * 1e-3) / 1e12,
                      "whole_step_frac": GF_TOTAL * 1e9 * B / (ms / K * 1e-3) / 1e12 / peak},
+        "roofline_hbm": hbm_rooflines(prof, B, final_boxes, peaks, peak_src),
+        "backbone": {"algorithmic_gflop_per_frame": GF_BACKBONE,
+                     "ms_per_step": round(prof["gemm_linear"][0] + prof["attention"][0] + prof["prompt"][0] + prof["norm_ce"][0], 4),
+                     "tflops": GF_BACKBONE * 1e9 * B / ((prof["gemm_linear"][0] + prof["attention"][0] + prof["prompt"][0]
+                                                        + prof["norm_ce"][0]) * 1e-3) / 1e12,
+                     "frac_of_peak": GF_BACKBONE * 1e9 * B / ((prof["gemm_linear"][0] + prof["attention"][0] + prof["prompt"][0]
+                                                              + prof["norm_ce"][0]) * 1e-3) / 1e12 / peak,
+                     "what": "patch embed + 12 blocks (linears, attention, prompt blocks, LayerNorms, CE) against the same peak"},
         "kernel_ms_per_step": {k: round(v[0], 4) for k, v in prof.items()},
         "kernel_share": {k: round(v[0] / step_ms_prof, 4) for k, v in prof.items()},
     }
@@ -269,6 +277,31 @@ def run_ours(args):
     print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
+
+
+GF_BACKBONE = 42.344      # patch embed + block linears + attention
+_N_TOK = [320, 320, 320, 320, 244, 244, 244, 190, 190, 190, 153, 153]      # tokens entering block i
+_N_MLP = [320, 320, 320, 244, 244, 244, 190, 190, 190, 153, 153, 153]      # tokens after block i's CE
+
+
+def hbm_rooflines(prof, B, boxes, peaks, peak_src):
+    """Achieved HBM GB/s of the memory-bound kernel classes: ALGORITHMIC bytes of one step (every operand read or
+    written once at the data types the engine uses: fp32 residual stream, fp16 branch outputs / GEMM operands, u8
+    frames) divided by the class's summed launch durations (CUDA-event pairs, un-graphed step).  Part of the fp32
+    residual stream stays in the 126 MB L2 between kernels, so DRAM traffic (profiles/*launches*.csv) is lower."""
+    hbm = float(peaks.get("hbm_gbs", 6650.0))
+    row = 768 * (4 + 2 + 4 + 2)                              # read x fp32 + branch fp16, write x fp32 + xn fp16
+    prompt = sum(_N_TOK[1:]) * row + 320 * 768 * (4 + 4 + 4 + 2)      # layers 1..11; layer 0: E_rgb, E_x -> x, xn
+    norm = sum(_N_MLP) * row + 153 * 768 * (4 + 2) + 256 * 768 * 2     # 12 x LN2 (+ CE gather), final norm + recover
+    cs = np.ceil(np.sqrt(np.maximum(boxes[:, 2] * boxes[:, 3], 0.0)) * 4.0)
+    crop = float(np.mean(np.minimum(cs, 630) * np.minimum(cs, 480) * 6)) + 6 * 256 * 256 * 2     # clipped rectangle + patch rows
+    out = {"peak": hbm, "unit": "GB/s", "peak_source": "%s hbm_gbs (copy bandwidth)" % peak_src, "kernels": {}}
+    for name, per_frame in (("prompt", prompt), ("norm_ce", norm), ("crop", crop)):
+        ms = prof[name][0]
+        gbs = per_frame * B / (ms * 1e-3) / 1e9 if ms > 0 else None
+        out["kernels"][name] = {"algorithmic_bytes_per_step": per_frame * B, "ms_per_step": round(ms, 4), "launches": prof[name][1],
+                                "achieved": gbs, "frac": gbs / hbm if gbs else None}
+    return out
 
 
 def gemm_traffic(B, n_gemm):

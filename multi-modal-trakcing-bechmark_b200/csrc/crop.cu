@@ -15,8 +15,28 @@
 
 namespace vipt {
 
-__constant__ float c_mean[3] = {0.485f, 0.456f, 0.406f};
-__constant__ float c_std[3] = {0.229f, 0.224f, 0.225f};
+// PreprocessorMM.process maps a u8 value to ((v / 255) - mean) / std in fp32 (data_utils.py:22-23); the patch rows are
+// fp16, so the whole map is a 3 x 256 table of fp16 values, computed once on the host with the same IEEE operations
+// (two fp32 divisions per channel value made the kernel issue-bound: 550 instructions per output pixel).
+static const float h_mean[3] = {0.485f, 0.456f, 0.406f};
+static const float h_std[3] = {0.229f, 0.224f, 0.225f};
+__device__ __align__(16) unsigned short g_norm_lut[3 * 256];
+
+int crop_prepare() {
+  static bool ready = false;
+  if (ready) return VIPT_OK;
+  unsigned short h[3 * 256];
+  for (int c = 0; c < 3; ++c)
+    for (int v = 0; v < 256; ++v) {
+      volatile float q = (float)v / 255.0f;          // volatile: each step rounded to fp32, no contraction
+      volatile float d = q - h_mean[c];
+      volatile float r = d / h_std[c];
+      h[c * 256 + v] = __half_as_ushort(__float2half_rn(r));
+    }
+  if (cudaMemcpyToSymbol(g_norm_lut, h, sizeof(h)) != cudaSuccess) return VIPT_ERR_LAUNCH;
+  ready = true;
+  return VIPT_OK;
+}
 
 struct Taps {
   int i0, i1;     // source indices in the padded crop (already clipped)
@@ -52,16 +72,32 @@ crop_kernel(const uint8_t* const* __restrict__ frames, const int* __restrict__ f
   pdl_wait();          // predecessor is the head of the previous step, which wrote the box state read here
   const int b = blockIdx.y;
   const int pix = blockIdx.x * 256 + threadIdx.x;
-  const int oy = pix / S, ox = pix % S;
-  const double bx = boxes[b * 4 + 0], by = boxes[b * 4 + 1], bw = boxes[b * 4 + 2], bh = boxes[b * 4 + 3];
-  const double csd = ceil(sqrt(bw * bh) * factor);
+  const int lgS = 31 - __clz(S);                     // S is 128 or 256
+  const int oy = pix >> lgS, ox = pix & (S - 1);
+  __shared__ __align__(16) unsigned short s_lut[3 * 256];
+  if (threadIdx.x < 96) reinterpret_cast<uint4*>(s_lut)[threadIdx.x] = reinterpret_cast<const uint4*>(g_norm_lut)[threadIdx.x];
+  // the crop geometry of a sequence (fp64 sqrt, two fp64 divisions) is evaluated by one thread per CTA: evaluated
+  // by every thread it made the kernel fp64-bound (87 us per 64-sequence step, 9 % of the HBM roofline)
+  __shared__ double s_geo[2];
+  __shared__ int s_gi[3];
+  if (threadIdx.x == 0) {
+    const double bx = boxes[b * 4 + 0], by = boxes[b * 4 + 1], bw = boxes[b * 4 + 2], bh = boxes[b * 4 + 3];
+    const double c = ceil(sqrt(bw * bh) * factor);
+    s_geo[0] = c;
+    s_geo[1] = c >= 1.0 ? 1.0 / ((double)S / (double)(int)c) : 0.0;
+    s_gi[0] = c >= 1.0 ? (int)c : 0;
+    s_gi[1] = (int)rint(bx + 0.5 * bw - c * 0.5);
+    s_gi[2] = (int)rint(by + 0.5 * bh - c * 0.5);
+  }
+  __syncthreads();
+  const double csd = s_geo[0];
   if (!(csd >= 1.0)) {           // 'Too small bounding box.' (processing_utils.py:34)
     if (pix == 0) atomicExch(err, VIPT_ERR_SMALL_BOX);
     return;
   }
-  const int cs = (int)csd;
-  const int x1 = (int)rint(bx + 0.5 * bw - csd * 0.5);
-  const int y1 = (int)rint(by + 0.5 * bh - csd * 0.5);
+  const int cs = s_gi[0];
+  const int x1 = s_gi[1];
+  const int y1 = s_gi[2];
   if (pix == 0 && geom) {
     geom[b * 4 + 0] = (double)x1; geom[b * 4 + 1] = (double)y1; geom[b * 4 + 2] = csd;
     geom[b * 4 + 3] = (double)S / csd;       // resize_factor (processing_utils.py:69)
@@ -71,12 +107,19 @@ crop_kernel(const uint8_t* const* __restrict__ frames, const int* __restrict__ f
   // padded-crop pixel (py, px) is image pixel (y1+py, x1+px) when 0 <= Y <= H-2 and 0 <= X <= W-2
   // (the `+1` in x2_pad / y2_pad drops the last row / column whenever the crop overhangs), else 0.
   int out[6];
+  const bool even = (reinterpret_cast<uintptr_t>(im) & 1) == 0;      // a pixel is 6 bytes: 2-byte aligned when the frame is
   auto load6 = [&](int py, int px, int (&v)[6]) {
     const int Y = y1 + py, X = x1 + px;
     if (Y >= 0 && Y <= H - 2 && X >= 0 && X <= W - 2) {
       const uint8_t* p = im + ((size_t)Y * W + X) * 6;
+      if (even) {                 // three 16-bit loads instead of six byte loads
+        const unsigned short* q = reinterpret_cast<const unsigned short*>(p);
+        const unsigned u0 = __ldg(q), u1 = __ldg(q + 1), u2 = __ldg(q + 2);
+        v[0] = u0 & 255; v[1] = u0 >> 8; v[2] = u1 & 255; v[3] = u1 >> 8; v[4] = u2 & 255; v[5] = u2 >> 8;
+      } else {
 #pragma unroll
-      for (int c = 0; c < 6; ++c) v[c] = p[c];
+        for (int c = 0; c < 6; ++c) v[c] = p[c];
+      }
     } else {
 #pragma unroll
       for (int c = 0; c < 6; ++c) v[c] = 0;
@@ -92,7 +135,7 @@ crop_kernel(const uint8_t* const* __restrict__ frames, const int* __restrict__ f
       out[c] = q + ((r == 3) || (r == 2 && (q & 1)));
     }
   } else {
-    const double scale = 1.0 / ((double)S / (double)cs);
+    const double scale = s_geo[1];
     const Taps tx = make_taps(ox, cs, scale, true);
     const Taps ty = make_taps(oy, cs, scale, false);
     int p00[6], p01[6], p10[6], p11[6];
@@ -109,11 +152,9 @@ crop_kernel(const uint8_t* const* __restrict__ frames, const int* __restrict__ f
   const int token = (oy >> 4) * tps + (ox >> 4);
   const int col = (oy & 15) * 16 + (ox & 15);
   const size_t row = (size_t)b * rows_per_seq + row_base + token;
+  unsigned short* dst = reinterpret_cast<unsigned short*>(apatch) + row * 768 + col;
 #pragma unroll
-  for (int c = 0; c < 6; ++c) {
-    const float v = (((float)out[c] / 255.0f) - c_mean[c % 3]) / c_std[c % 3];
-    apatch[(size_t)(c / 3) * group_stride + row * 768 + (c % 3) * 256 + col] = to_op(v);
-  }
+  for (int c = 0; c < 6; ++c) dst[(size_t)(c / 3) * group_stride + (c % 3) * 256] = s_lut[(c % 3) * 256 + out[c]];
 }
 
 // fp32 NCHW (B,6,S,S) -> patch-major fp16 rows (the forward(template, search) entry).
@@ -135,6 +176,7 @@ patchify_kernel(const float* __restrict__ img, int S, int row_base, int rows_per
 int launch_crop(const uint8_t* const* frames, const int* frame_hw, const double* boxes, double factor, int S,
                 int row_base, int rows_per_seq, void* apatch, int64_t group_stride, double* geom, int* err, int B,
                 cudaStream_t st) {
+  if ((S != 128 && S != 256) || crop_prepare()) return VIPT_ERR_ARG;
   dim3 grid(S * S / 256, B);
   const cudaError_t e_ = launch_pdl(crop_kernel, grid, 256, 0, st, frames, frame_hw, boxes, factor, S, row_base, rows_per_seq,
                                     reinterpret_cast<op_t*>(apatch), group_stride, geom, err);

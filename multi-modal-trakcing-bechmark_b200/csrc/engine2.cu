@@ -77,6 +77,7 @@ int Engine::finalize_buffers() {
     for (size_t i = 0; i < RH; ++i) id[i] = (int)(i % kLensX);
     CK(cudaMemcpy(ident, id.data(), RH * 4, cudaMemcpyHostToDevice));
     CK(cudaMemset(err, 0, 4));
+    RET(crop_prepare());
     CK(cudaMemset(removed, 0, 3 * RH * 4));
   }
   // ---- GEMM / attention plans
