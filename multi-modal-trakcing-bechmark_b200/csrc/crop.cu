@@ -63,7 +63,9 @@ __device__ __forceinline__ Taps make_taps(int d, int src, double scale, bool hor
   return t;
 }
 
-// grid: (S*S/256, B); one thread per output pixel, all 6 channels.
+// grid: (S*S/(8*256), B); one thread per 8 consecutive output pixels of a row, all 6 channels: the vertical taps, the
+// row pointers and the patch-row address are shared by the 8 pixels and each channel leaves as one 16-byte store.
+constexpr int kCropPix = 8;
 __global__ void __launch_bounds__(256)
 crop_kernel(const uint8_t* const* __restrict__ frames, const int* __restrict__ frame_hw,
             const double* __restrict__ boxes, double factor, int S, int row_base, int rows_per_seq,
@@ -71,9 +73,9 @@ crop_kernel(const uint8_t* const* __restrict__ frames, const int* __restrict__ f
   pdl_trigger();       // programmatic dependent launch protocol (sm100_ptx.cuh); first kernel of a step: its
   pdl_wait();          // predecessor is the head of the previous step, which wrote the box state read here
   const int b = blockIdx.y;
-  const int pix = blockIdx.x * 256 + threadIdx.x;
-  const int lgS = 31 - __clz(S);                     // S is 128 or 256
-  const int oy = pix >> lgS, ox = pix & (S - 1);
+  const int unit = blockIdx.x * 256 + threadIdx.x;   // over S * S / 8
+  const int lgU = 31 - __clz(S) - 3;                 // S is 128 or 256: 16 or 32 units per row
+  const int oy = unit >> lgU, ox0 = (unit & ((S >> 3) - 1)) << 3;
   __shared__ __align__(16) unsigned short s_lut[3 * 256];
   if (threadIdx.x < 96) reinterpret_cast<uint4*>(s_lut)[threadIdx.x] = reinterpret_cast<const uint4*>(g_norm_lut)[threadIdx.x];
   // the crop geometry of a sequence (fp64 sqrt, two fp64 divisions) is evaluated by one thread per CTA: evaluated
@@ -92,13 +94,13 @@ crop_kernel(const uint8_t* const* __restrict__ frames, const int* __restrict__ f
   __syncthreads();
   const double csd = s_geo[0];
   if (!(csd >= 1.0)) {           // 'Too small bounding box.' (processing_utils.py:34)
-    if (pix == 0) atomicExch(err, VIPT_ERR_SMALL_BOX);
+    if (unit == 0) atomicExch(err, VIPT_ERR_SMALL_BOX);
     return;
   }
   const int cs = s_gi[0];
   const int x1 = s_gi[1];
   const int y1 = s_gi[2];
-  if (pix == 0 && geom) {
+  if (unit == 0 && geom) {
     geom[b * 4 + 0] = (double)x1; geom[b * 4 + 1] = (double)y1; geom[b * 4 + 2] = csd;
     geom[b * 4 + 3] = (double)S / csd;       // resize_factor (processing_utils.py:69)
   }
@@ -106,12 +108,11 @@ crop_kernel(const uint8_t* const* __restrict__ frames, const int* __restrict__ f
   const uint8_t* im = frames[b];
   // padded-crop pixel (py, px) is image pixel (y1+py, x1+px) when 0 <= Y <= H-2 and 0 <= X <= W-2
   // (the `+1` in x2_pad / y2_pad drops the last row / column whenever the crop overhangs), else 0.
-  int out[6];
   const bool even = (reinterpret_cast<uintptr_t>(im) & 1) == 0;      // a pixel is 6 bytes: 2-byte aligned when the frame is
-  auto load6 = [&](int py, int px, int (&v)[6]) {
-    const int Y = y1 + py, X = x1 + px;
-    if (Y >= 0 && Y <= H - 2 && X >= 0 && X <= W - 2) {
-      const uint8_t* p = im + ((size_t)Y * W + X) * 6;
+  auto load6 = [&](const uint8_t* rowp, bool row_ok, int px, int (&v)[6]) {
+    const int X = x1 + px;
+    if (row_ok && X >= 0 && X <= W - 2) {
+      const uint8_t* p = rowp + (size_t)X * 6;
       if (even) {                 // three 16-bit loads instead of six byte loads
         const unsigned short* q = reinterpret_cast<const unsigned short*>(p);
         const unsigned u0 = __ldg(q), u1 = __ldg(q + 1), u2 = __ldg(q + 2);
@@ -125,36 +126,56 @@ crop_kernel(const uint8_t* const* __restrict__ frames, const int* __restrict__ f
       for (int c = 0; c < 6; ++c) v[c] = 0;
     }
   };
-  if (cs == 2 * S) {
-    int a[6], bb[6], c2[6], d[6];
-    load6(2 * oy, 2 * ox, a); load6(2 * oy, 2 * ox + 1, bb); load6(2 * oy + 1, 2 * ox, c2); load6(2 * oy + 1, 2 * ox + 1, d);
+  const bool area = cs == 2 * S;
+  const double scale = s_geo[1];
+  Taps ty;
+  if (area) { ty.i0 = 2 * oy; ty.i1 = 2 * oy + 1; ty.c0 = ty.c1 = 0; }
+  else ty = make_taps(oy, cs, scale, false);
+  const int Y0 = y1 + ty.i0, Y1 = y1 + ty.i1;
+  const bool ok0 = Y0 >= 0 && Y0 <= H - 2, ok1 = Y1 >= 0 && Y1 <= H - 2;
+  const uint8_t* r0p = im + (size_t)(ok0 ? Y0 : 0) * W * 6;
+  const uint8_t* r1p = im + (size_t)(ok1 ? Y1 : 0) * W * 6;
+  uint32_t o[6][kCropPix / 2];
 #pragma unroll
-    for (int c = 0; c < 6; ++c) {
-      const int sum = a[c] + bb[c] + c2[c] + d[c];
-      const int q = sum >> 2, r = sum & 3;
-      out[c] = q + ((r == 3) || (r == 2 && (q & 1)));
-    }
-  } else {
-    const double scale = s_geo[1];
-    const Taps tx = make_taps(ox, cs, scale, true);
-    const Taps ty = make_taps(oy, cs, scale, false);
-    int p00[6], p01[6], p10[6], p11[6];
-    load6(ty.i0, tx.i0, p00); load6(ty.i0, tx.i1, p01); load6(ty.i1, tx.i0, p10); load6(ty.i1, tx.i1, p11);
+  for (int c = 0; c < 6; ++c)
 #pragma unroll
-    for (int c = 0; c < 6; ++c) {
-      const int r0 = p00[c] * tx.c0 + p01[c] * tx.c1;
-      const int r1 = p10[c] * tx.c0 + p11[c] * tx.c1;
-      int v = (((ty.c0 * (r0 >> 4)) >> 16) + ((ty.c1 * (r1 >> 4)) >> 16) + 2) >> 2;
-      out[c] = min(max(v, 0), 255);
+    for (int q = 0; q < kCropPix / 2; ++q) o[c][q] = 0u;
+#pragma unroll
+  for (int px = 0; px < kCropPix; ++px) {
+    const int ox = ox0 + px;
+    int out[6];
+    if (area) {
+      int a[6], bb[6], c2[6], d[6];
+      load6(r0p, ok0, 2 * ox, a); load6(r0p, ok0, 2 * ox + 1, bb); load6(r1p, ok1, 2 * ox, c2); load6(r1p, ok1, 2 * ox + 1, d);
+#pragma unroll
+      for (int c = 0; c < 6; ++c) {
+        const int sum = a[c] + bb[c] + c2[c] + d[c];
+        const int q = sum >> 2, r = sum & 3;
+        out[c] = q + ((r == 3) || (r == 2 && (q & 1)));
+      }
+    } else {
+      const Taps tx = make_taps(ox, cs, scale, true);
+      int p00[6], p01[6], p10[6], p11[6];
+      load6(r0p, ok0, tx.i0, p00); load6(r0p, ok0, tx.i1, p01); load6(r1p, ok1, tx.i0, p10); load6(r1p, ok1, tx.i1, p11);
+#pragma unroll
+      for (int c = 0; c < 6; ++c) {
+        const int r0 = p00[c] * tx.c0 + p01[c] * tx.c1;
+        const int r1 = p10[c] * tx.c0 + p11[c] * tx.c1;
+        int v = (((ty.c0 * (r0 >> 4)) >> 16) + ((ty.c1 * (r1 >> 4)) >> 16) + 2) >> 2;
+        out[c] = min(max(v, 0), 255);
+      }
     }
+#pragma unroll
+    for (int c = 0; c < 6; ++c) o[c][px >> 1] |= (uint32_t)s_lut[(c % 3) * 256 + out[c]] << (16 * (px & 1));
   }
   const int tps = S / 16;
-  const int token = (oy >> 4) * tps + (ox >> 4);
-  const int col = (oy & 15) * 16 + (ox & 15);
+  const int token = (oy >> 4) * tps + (ox0 >> 4);
+  const int col = (oy & 15) * 16 + (ox0 & 15);        // multiple of 8: 16-byte aligned in the fp16 patch row
   const size_t row = (size_t)b * rows_per_seq + row_base + token;
   unsigned short* dst = reinterpret_cast<unsigned short*>(apatch) + row * 768 + col;
 #pragma unroll
-  for (int c = 0; c < 6; ++c) dst[(size_t)(c / 3) * group_stride + (c % 3) * 256] = s_lut[(c % 3) * 256 + out[c]];
+  for (int c = 0; c < 6; ++c)
+    *reinterpret_cast<uint4*>(dst + (size_t)(c / 3) * group_stride + (c % 3) * 256) = make_uint4(o[c][0], o[c][1], o[c][2], o[c][3]);
 }
 
 // fp32 NCHW (B,6,S,S) -> patch-major fp16 rows (the forward(template, search) entry).
@@ -177,7 +198,8 @@ int launch_crop(const uint8_t* const* frames, const int* frame_hw, const double*
                 int row_base, int rows_per_seq, void* apatch, int64_t group_stride, double* geom, int* err, int B,
                 cudaStream_t st) {
   if ((S != 128 && S != 256) || crop_prepare()) return VIPT_ERR_ARG;
-  dim3 grid(S * S / 256, B);
+  if ((group_stride & 7) || (reinterpret_cast<uintptr_t>(apatch) & 15)) return VIPT_ERR_ARG;      // 16-byte stores
+  dim3 grid(S * S / (kCropPix * 256), B);
   const cudaError_t e_ = launch_pdl(crop_kernel, grid, 256, 0, st, frames, frame_hw, boxes, factor, S, row_base, rows_per_seq,
                                     reinterpret_cast<op_t*>(apatch), group_stride, geom, err);
   return e_ == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
