@@ -142,30 +142,47 @@ prompt_coop_kernel(float* __restrict__ x, const op_t* __restrict__ delta, int B,
     __syncwarp();
     if (lane == 0 && r0 + 2 * kWarps < row_hi)   // next pair of this warp: in flight during the math below
       pc_prefetch(x, delta, (size_t)(r0 + 2 * kWarps), min(2, row_hi - (r0 + 2 * kWarps)), slot, bar);
-    float mean[2], q[2] = {0.f, 0.f}, dot[2][8];
+    // The 768 -> 8 projection is 2 x 6144 FMAs per row pair and lane-for-lane the bulk of this kernel's instructions:
+    // packed fp32x2 FMAs on (x, y) / (z, w) column pairs (the float4 halves are register pairs already) halve them.
+    float mean[2], q[2], dot[2][8];
+    uint64_t q2[2], dot2[2][8], nm2[2];
 #pragma unroll
     for (int i = 0; i < 2; ++i) {
       float s = 0.f;
 #pragma unroll
       for (int j = 0; j < 6; ++j) s += v[i][j].x + v[i][j].y + v[i][j].z + v[i][j].w;
       mean[i] = pc_warp_sum(s) * (1.0f / D);
+      nm2[i] = pk2(-mean[i], -mean[i]);
+      q2[i] = 0ull;
 #pragma unroll
-      for (int k = 0; k < 8; ++k) dot[i][k] = 0.f;
+      for (int k = 0; k < 8; ++k) dot2[i][k] = 0ull;
     }
 #pragma unroll
     for (int j = 0; j < 6; ++j) {
-      float4 a[2];
+      uint64_t a2[2][2];
 #pragma unroll
       for (int i = 0; i < 2; ++i) {
-        a[i] = make_float4(v[i][j].x - mean[i], v[i][j].y - mean[i], v[i][j].z - mean[i], v[i][j].w - mean[i]);
-        q[i] += a[i].x * a[i].x + a[i].y * a[i].y + a[i].z * a[i].z + a[i].w * a[i].w;
+        a2[i][0] = add2(pk2(v[i][j].x, v[i][j].y), nm2[i]);
+        a2[i][1] = add2(pk2(v[i][j].z, v[i][j].w), nm2[i]);
+        q2[i] = fma2(a2[i][0], a2[i][0], q2[i]);
+        q2[i] = fma2(a2[i][1], a2[i][1], q2[i]);
       }
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
         const float4 w = s_wa[k * 192 + lane + 32 * j];
+        const uint64_t w01 = pk2(w.x, w.y), w23 = pk2(w.z, w.w);
 #pragma unroll
-        for (int i = 0; i < 2; ++i) dot[i][k] += w.x * a[i].x + w.y * a[i].y + w.z * a[i].z + w.w * a[i].w;
+        for (int i = 0; i < 2; ++i) {
+          dot2[i][k] = fma2(w01, a2[i][0], dot2[i][k]);
+          dot2[i][k] = fma2(w23, a2[i][1], dot2[i][k]);
+        }
       }
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      q[i] = hsum2(q2[i]);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) dot[i][k] = hsum2(dot2[i][k]);
     }
 #pragma unroll
     for (int i = 0; i < 2; ++i) {
@@ -283,24 +300,37 @@ prompt_coop_kernel(float* __restrict__ x, const op_t* __restrict__ delta, int B,
       for (int i = 0; i < 2; ++i)
 #pragma unroll
         for (int k = 0; k < 8; ++k) f[i][k] = __shfl_sync(0xffffffffu, fk, i * 8 + k);
+      uint64_t f2[2][8], s2[2] = {0ull, 0ull};    // packed fp32x2 FMAs for the 8 -> 768 projection (see phase 1)
+#pragma unroll
+      for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int k = 0; k < 8; ++k) f2[i][k] = pk2(f[i][k], f[i][k]);
 #pragma unroll
       for (int j = 0; j < 6; ++j) {
         const float4 bias = s_b1[lane + 32 * j];
-        float4 p[2] = {bias, bias};
+        uint64_t p2[2][2];
+#pragma unroll
+        for (int i = 0; i < 2; ++i) { p2[i][0] = pk2(bias.x, bias.y); p2[i][1] = pk2(bias.z, bias.w); }
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
           const float4 w = s_w1[k * 192 + lane + 32 * j];
+          const uint64_t w01 = pk2(w.x, w.y), w23 = pk2(w.z, w.w);
 #pragma unroll
           for (int i = 0; i < 2; ++i) {
-            p[i].x += w.x * f[i][k]; p[i].y += w.y * f[i][k]; p[i].z += w.z * f[i][k]; p[i].w += w.w * f[i][k];
+            p2[i][0] = fma2(w01, f2[i][k], p2[i][0]);
+            p2[i][1] = fma2(w23, f2[i][k], p2[i][1]);
           }
         }
 #pragma unroll
         for (int i = 0; i < 2; ++i) {
-          v[i][j].x += p[i].x; v[i][j].y += p[i].y; v[i][j].z += p[i].z; v[i][j].w += p[i].w;
-          s[i] += v[i][j].x + v[i][j].y + v[i][j].z + v[i][j].w;
+          const uint64_t v01 = add2(pk2(v[i][j].x, v[i][j].y), p2[i][0]), v23 = add2(pk2(v[i][j].z, v[i][j].w), p2[i][1]);
+          upk2(v01, v[i][j].x, v[i][j].y);
+          upk2(v23, v[i][j].z, v[i][j].w);
+          s2[i] = add2(s2[i], add2(v01, v23));
         }
       }
+#pragma unroll
+      for (int i = 0; i < 2; ++i) s[i] += hsum2(s2[i]);
       float mean[2], rstd[2];
 #pragma unroll
       for (int i = 0; i < 2; ++i) {
