@@ -38,6 +38,17 @@ constexpr int kSmemBytes = 2 * 8 * D * 4 + 3 * D * 4 + kFoldFloats * 4 + kMaxSeq
                            kWarps * kSlotBytes + (kWarps + 1) * 8 + 64;
 }  // namespace pc
 
+// two independent butterflies interleaved: a 5-step shuffle chain is pure latency for a warp (this kernel runs 4 warps
+// per scheduler; the reductions were its largest stall), two chains in flight cost the same time as one
+__device__ __forceinline__ void pc_warp_sum2(float& a, float& b) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ta = __shfl_xor_sync(0xffffffffu, a, o), tb = __shfl_xor_sync(0xffffffffu, b, o);
+    a += ta;
+    b += tb;
+  }
+}
+
 __device__ __forceinline__ float pc_warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -146,12 +157,18 @@ prompt_coop_kernel(float* __restrict__ x, const op_t* __restrict__ delta, int B,
     // packed fp32x2 FMAs on (x, y) / (z, w) column pairs (the float4 halves are register pairs already) halve them.
     float mean[2], q[2], dot[2][8];
     uint64_t q2[2], dot2[2][8], nm2[2];
+    {
+      float s[2] = {0.f, 0.f};
+#pragma unroll
+      for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int j = 0; j < 6; ++j) s[i] += v[i][j].x + v[i][j].y + v[i][j].z + v[i][j].w;
+      pc_warp_sum2(s[0], s[1]);
+      mean[0] = s[0] * (1.0f / D);
+      mean[1] = s[1] * (1.0f / D);
+    }
 #pragma unroll
     for (int i = 0; i < 2; ++i) {
-      float s = 0.f;
-#pragma unroll
-      for (int j = 0; j < 6; ++j) s += v[i][j].x + v[i][j].y + v[i][j].z + v[i][j].w;
-      mean[i] = pc_warp_sum(s) * (1.0f / D);
       nm2[i] = pk2(-mean[i], -mean[i]);
       q2[i] = 0ull;
 #pragma unroll
@@ -184,9 +201,10 @@ prompt_coop_kernel(float* __restrict__ x, const op_t* __restrict__ delta, int B,
 #pragma unroll
       for (int k = 0; k < 8; ++k) dot[i][k] = hsum2(dot2[i][k]);
     }
+    pc_warp_sum2(q[0], q[1]);
 #pragma unroll
     for (int i = 0; i < 2; ++i) {
-      const float rstd = rsqrtf(pc_warp_sum(q[i]) * (1.0f / D) + kLnEps);
+      const float rstd = rsqrtf(q[i] * (1.0f / D) + kLnEps);
       // transposed butterfly: 8 sums over 32 lanes in 9 shuffles; lane l ends with sum #(l >> 2)
       float a4[4], a2[2];
 #pragma unroll
@@ -282,9 +300,13 @@ prompt_coop_kernel(float* __restrict__ x, const op_t* __restrict__ delta, int B,
           float var = s_fold[kC0], a = s_fold[kA0 + k];
 #pragma unroll
           for (int p = 0; p < 8; ++p) {
-            float g = 0.f;
+            float g = 0.f, g1 = 0.f;          // two chains: this runs on 16 lanes per warp and is pure latency
 #pragma unroll
-            for (int qq = 0; qq < 8; ++qq) g += s_fold[kG + p * 8 + qq] * f[qq];
+            for (int qq = 0; qq < 8; qq += 2) {
+              g += s_fold[kG + p * 8 + qq] * f[qq];
+              g1 += s_fold[kG + p * 8 + qq + 1] * f[qq + 1];
+            }
+            g += g1;
             var += f[p] * (g + 2.0f * s_fold[kH + p]);
             a += s_fold[kA + k * 8 + p] * f[p];
           }
@@ -331,7 +353,7 @@ prompt_coop_kernel(float* __restrict__ x, const op_t* __restrict__ delta, int B,
       }
 #pragma unroll
       for (int i = 0; i < 2; ++i) s[i] += hsum2(s2[i]);
-      float mean[2], rstd[2];
+      float mean[2], rstd[2], qv[2] = {0.f, 0.f};
 #pragma unroll
       for (int i = 0; i < 2; ++i) {
         if (i == 1 && !two) break;
@@ -339,15 +361,20 @@ prompt_coop_kernel(float* __restrict__ x, const op_t* __restrict__ delta, int B,
         float4* xo = reinterpret_cast<float4*>(x + row * D);
 #pragma unroll
         for (int j = 0; j < 6; ++j) xo[lane + 32 * j] = v[i][j];
-        mean[i] = pc_warp_sum(s[i]) * (1.0f / D);
-        float q = 0.f;
+      }
+      pc_warp_sum2(s[0], s[1]);                  // both rows' butterflies in flight together (row 1 is zeros if !two)
+      mean[0] = s[0] * (1.0f / D);
+      mean[1] = s[1] * (1.0f / D);
+#pragma unroll
+      for (int i = 0; i < 2; ++i)
 #pragma unroll
         for (int j = 0; j < 6; ++j) {
           const float a0 = v[i][j].x - mean[i], a1 = v[i][j].y - mean[i], a2 = v[i][j].z - mean[i], a3 = v[i][j].w - mean[i];
-          q += a0 * a0 + a1 * a1 + a2 * a2 + a3 * a3;
+          qv[i] += a0 * a0 + a1 * a1 + a2 * a2 + a3 * a3;
         }
-        rstd[i] = rsqrtf(pc_warp_sum(q) * (1.0f / D) + kLnEps);
-      }
+      pc_warp_sum2(qv[0], qv[1]);
+      rstd[0] = rsqrtf(qv[0] * (1.0f / D) + kLnEps);
+      rstd[1] = rsqrtf(qv[1] * (1.0f / D) + kLnEps);
 #pragma unroll
       for (int j = 0; j < 6; ++j) {              // norm1 scale / shift read once for both rows
         const float4 g = s_g1[lane + 32 * j];
