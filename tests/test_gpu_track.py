@@ -149,6 +149,7 @@ def test_host_roi_upload_matches_device_frames(pinned):
     ("vipt_deep", "rgbt", 64, (0, 1, 4)),       # BASELINE.json configs[1]: 64 LasHeR-shaped sequences per B200
     ("vipt_deep", "rgbe", 64, (2,)),            # configs[2]: VisEvent-shaped, the per-GPU shard of the 2/4/8-GPU runs
     ("vipt_shaw", "rgbd", 32, (12, 14, 15)),    # configs[3]: shallow prompt, 256 sequences over 8 GPUs = 32 per GPU
+    ("vipt_deep", "rgbt", 128, (0, 1, 4)),      # configs[4]: 1024 sequences over 8 GPUs = 128 per GPU
 ])
 def test_full_size_batch_against_oracle(ptype, modality, B, checked):
     """BASELINE.json configs at full per-GPU size: B concurrent sequences in one engine (the 2-CTA GEMM, persistent
