@@ -84,6 +84,9 @@ int vipt_engine_results(void* engine, double* boxes_host, float* scores_host, vo
  * from host memory, the rectangle evaluated on the device from the box state, so up to 4 steps may be enqueued
  * before their results are collected; bytes_copied is then -1 at enqueue and reported by collect.  Pageable frames:
  * one 2-D copy per sequence, rectangle from the host mirror of the state (whole frame when the mirror is stale).
+ * LIFETIME: the gather kernel and the speculative uploads read the frames asynchronously, after track_host has
+ * returned.  Every frame passed to vipt_engine_track_host must stay valid and unmodified until THAT step has been
+ * collected (vipt_engine_collect) or the stream has been synchronised through vipt_engine_results.
  * collect returns the boxes / scores of the OLDEST uncollected track_host step (VIPT_ERR_STATE when there is none).
  * set_state overrides the box state (teacher-forced evaluation). */
 int vipt_engine_init_host(void* engine, const void* const* host_frames, const int* hw_host, const double* boxes_host,

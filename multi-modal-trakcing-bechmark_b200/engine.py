@@ -1,5 +1,6 @@
 """Thin Python owner of a native engine (libvipt_b200.so).  torch is used only for device memory,
 streams and host<->device copies; every computation happens in the CUDA library."""
+import collections
 import ctypes
 
 import numpy as np
@@ -56,6 +57,9 @@ class NativeEngine:
             _lib.check(self.L.vipt_engine_finalize(self.h, self.batch, 1 if prompt_type == "vipt_deep" else 0),
                        "vipt_engine_finalize")
         self._frames_keepalive = None
+        # host frames of every enqueued, not yet collected track_host step: the gather kernel and the speculative
+        # uploads read them asynchronously (csrc/engine3.cu), so they must outlive the call that enqueued them
+        self._host_keepalive = collections.deque()
 
     def __del__(self):
         try:
@@ -107,6 +111,7 @@ class NativeEngine:
     def init_sequences_host(self, host_ptrs, hw, boxes, keepalive=None):
         """host_ptrs: B host addresses of uint8 (H,W,6) frames; hw (B,2) int32; boxes (B,4)."""
         self._frames_keepalive = keepalive
+        self._host_keepalive.clear()
         ptrs = (ctypes.c_void_p * self.batch)(*host_ptrs)
         hw = np.ascontiguousarray(np.asarray(hw, np.int32).reshape(self.batch, 2))
         bx = np.ascontiguousarray(np.asarray(boxes, np.float64).reshape(self.batch, 4))
@@ -114,8 +119,10 @@ class NativeEngine:
                                                 bx.ctypes.data_as(ctypes.c_void_p), self._sp()), "vipt_engine_init_host")
 
     def track_host(self, host_ptrs, use_graph=True, keepalive=None):
-        """Upload the search rectangles of B host frames and enqueue one step; returns bytes uploaded."""
-        self._frames_keepalive = keepalive
+        """Upload the search rectangles of B host frames and enqueue one step; returns bytes uploaded.
+        The frames must stay valid and unmodified until this step has been collected (include/vipt_b200.h); the
+        `keepalive` objects are held until then."""
+        self._host_keepalive.append(keepalive)
         ptrs = (ctypes.c_void_p * self.batch)(*host_ptrs)
         n = ctypes.c_int64(0)
         _lib.check(self.L.vipt_engine_track_host(self.h, ptrs, int(use_graph), ctypes.byref(n), self._sp()),
@@ -129,6 +136,8 @@ class NativeEngine:
         n = ctypes.c_int64(0)
         _lib.check(self.L.vipt_engine_collect(self.h, boxes.ctypes.data_as(ctypes.c_void_p),
                                               scores.ctypes.data_as(ctypes.c_void_p), ctypes.byref(n)), "vipt_engine_collect")
+        if self._host_keepalive:
+            self._host_keepalive.popleft()
         return boxes, scores, n.value
 
     def set_state(self, boxes):
@@ -158,4 +167,5 @@ class NativeEngine:
         _lib.check(self.L.vipt_engine_results(self.h, boxes.ctypes.data_as(ctypes.c_void_p),
                                               scores.ctypes.data_as(ctypes.c_void_p), self._sp()),
                    "vipt_engine_results")
+        self._host_keepalive.clear()        # the stream was synchronised: every enqueued step has read its frames
         return boxes, scores

@@ -36,6 +36,21 @@ def _xavier(g, shape):
     return (torch.rand(shape, generator=g) * 2 - 1) * a
 
 
+# Named weight sets.  "flat": the reference's default init (qkv std 0.02): attention is almost uniform, so the
+# candidate-elimination scores of all search tokens sit within a few 1e-4 of 1/N of each other and most frames are
+# decided by differences below fp16-operand resolution.  "peaked": qkv std 0.06 gives attention logits of std ~2.9
+# (max ~15; row entropy ~4.0 nats against 5.8 for uniform attention, CE scores spread over 2.5 decades), the range a
+# trained ViT works in.  Larger values are not usable as a parity workload: the random network turns chaotic (logit
+# std 11 at qkv std 0.12: near-argmax attention, where rounding the GEMM operands of the fp32 reference itself to
+# 16 bits changes the CE scores by ~100 % and the score map by ~50 %; measured with oracle.vipt_oracle.OPERAND_ROUND).
+WEIGHT_SETS = {"flat": 0.02, "peaked": 0.06}
+
+
+def weight_set(name: str, prompt_type: str = "vipt_deep", seed: int = 0):
+    """state_dict of a named weight set (WEIGHT_SETS)."""
+    return synthetic_state_dict(prompt_type, seed, qkv_std=WEIGHT_SETS[name])
+
+
 def synthetic_state_dict(prompt_type: str = "vipt_deep", seed: int = 0, qkv_std: float = 0.02):
     """name -> fp32 tensor, in the reference's state_dict order."""
     assert prompt_type in ("vipt_deep", "vipt_shaw")

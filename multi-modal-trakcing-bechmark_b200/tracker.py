@@ -62,11 +62,21 @@ class BatchedViPTTracker:
         else:
             frames = [im if (isinstance(im, torch.Tensor) and im.is_cuda) else
                       torch.from_numpy(np.ascontiguousarray(im)).to(self.engine.device) for im in images]
+            self._order_after_producer(frames)
             self.engine.init_sequences(frames, boxes)
         self.frame_id = 0
         self.state = boxes.copy()
         self.h2d_bytes = 0
         self._pending_host = 0
+
+    def _order_after_producer(self, frames):
+        """Device frames are usually produced on the caller's current stream (frames.get_x_frame, .to(device)); the
+        engine runs on its own stream, so it must wait for the producer, and the caching allocator must not hand the
+        frame memory out again before the engine's crop kernel has read it."""
+        es = self.engine.stream
+        es.wait_stream(torch.cuda.current_stream(self.engine.device))
+        for f in frames:
+            f.record_stream(es)
 
     def set_state(self, boxes):
         """Override the box state of every sequence (teacher-forced evaluation)."""
@@ -85,6 +95,7 @@ class BatchedViPTTracker:
         else:
             frames = [im if (isinstance(im, torch.Tensor) and im.is_cuda) else
                       torch.from_numpy(np.ascontiguousarray(im)).to(self.engine.device) for im in images]
+            self._order_after_producer(frames)
             with torch.cuda.stream(self.engine.stream):
                 ptrs = torch.tensor([f.data_ptr() for f in frames], dtype=torch.int64).pin_memory().to(
                     self.engine.device, non_blocking=True)

@@ -42,6 +42,17 @@ SEARCH_FACTOR = 4.0
 TEMPLATE_FACTOR = 2.0
 
 
+# Optional operand rounding, used ONLY by the tests of the parity harness itself (tests/test_parity_harness.py): with
+# OPERAND_ROUND = lambda t: t.half().float() the GEMM / attention operands are rounded the way a 16-bit tensor-core
+# implementation rounds them, which gives a CPU stand-in for "an implementation with fp16-operand error".  None = the
+# exact fp32 restatement (every parity number is taken against that).
+OPERAND_ROUND = None
+
+
+def _q(t):
+    return t if OPERAND_ROUND is None else OPERAND_ROUND(t)
+
+
 def _ln(x, sd, prefix):
     return F.layer_norm(x, (x.shape[-1],), sd[prefix + ".weight"], sd[prefix + ".bias"], LN_EPS)
 
@@ -68,17 +79,19 @@ def _prompt_block(sd, i, a_tok, d_tok):
 def _attention(x, sd, prefix):
     """attn.py:33-59; returns (proj output, probs (B, H, N, N))."""
     B, N, C = x.shape
-    qkv = F.linear(x, sd[prefix + ".qkv.weight"], sd[prefix + ".qkv.bias"])
+    qkv = _q(F.linear(_q(x), _q(sd[prefix + ".qkv.weight"]), sd[prefix + ".qkv.bias"]))
     qkv = qkv.reshape(B, N, 3, NUM_HEADS, C // NUM_HEADS).permute(2, 0, 3, 1, 4)
     q, k, v = qkv[0], qkv[1], qkv[2]
     attn = (q @ k.transpose(-2, -1)) * ((C // NUM_HEADS) ** -0.5)
     attn = attn.softmax(dim=-1)
-    y = (attn @ v).transpose(1, 2).reshape(B, N, C)
-    return F.linear(y, sd[prefix + ".proj.weight"], sd[prefix + ".proj.bias"]), attn
+    y = (_q(attn) @ v).transpose(1, 2).reshape(B, N, C)
+    return _q(F.linear(_q(y), _q(sd[prefix + ".proj.weight"]), sd[prefix + ".proj.bias"])), attn
 
 
-def _candidate_elimination(attn, tokens, lens_t, keep_ratio, global_index, box_mask_z):
-    """attn_blocks.py:21-75."""
+def _candidate_elimination(attn, tokens, lens_t, keep_ratio, global_index, box_mask_z, forced_removed=None):
+    """attn_blocks.py:21-75.  `forced_removed` (B, n_removed) raster positions, test-only: the removal decision is
+    taken from the caller instead of the top-k (parity protocol: the stages after a near-tie decision are compared
+    against the reference arithmetic run on the implementation's kept set); order stays score-descending."""
     lens_s = attn.shape[-1] - lens_t
     bs, hn = attn.shape[:2]
     lens_keep = math.ceil(keep_ratio * lens_s)
@@ -90,6 +103,11 @@ def _candidate_elimination(attn, tokens, lens_t, keep_ratio, global_index, box_m
         attn_t = attn_t[m].view(bs, hn, -1, lens_s)
     score = attn_t.mean(dim=2).mean(dim=1)                        # (B, L_s)
     sorted_attn, indices = torch.sort(score, dim=1, descending=True)
+    if forced_removed is not None:
+        gone = (global_index.gather(1, indices).unsqueeze(-1) == forced_removed.unsqueeze(1)).any(-1)   # sorted order
+        assert int(gone.sum(1).min()) == int(gone.sum(1).max()) == lens_s - lens_keep
+        order = torch.sort(gone.to(torch.int8), dim=1, stable=True).indices      # kept first, both score-descending
+        indices = indices.gather(1, order)
     topk_idx, non_topk_idx = indices[:, :lens_keep], indices[:, lens_keep:]
     keep_index = global_index.gather(1, topk_idx)
     removed_index = global_index.gather(1, non_topk_idx)
@@ -111,7 +129,7 @@ def _scatter_full(x_s, global_index_s, removed, lens_x):
     return torch.zeros_like(x_s).scatter_(1, index_all.unsqueeze(-1).expand(B, -1, C), x_s)
 
 
-def backbone_forward(sd, z_img, x_img, ce_template_mask, prompt_type="vipt_deep", trace=None):
+def backbone_forward(sd, z_img, x_img, ce_template_mask, prompt_type="vipt_deep", trace=None, forced_removed=None):
     """VisionTransformerCE.forward_features.  z_img (B,6,128,128), x_img (B,6,256,256) fp32."""
     bb = "backbone."
     B = x_img.shape[0]
@@ -130,6 +148,7 @@ def backbone_forward(sd, z_img, x_img, ce_template_mask, prompt_type="vipt_deep"
     gi_s = torch.arange(lens_x, dtype=torch.int64).repeat(B, 1)
     removed = []
     ce_scores = []
+    ce_index = []          # raster position of every search slot entering each CE stage (ce_scores column order)
     attn = None
     for i in range(12):
         if i >= 1 and prompt_type == "vipt_deep":                  # :268-310
@@ -149,16 +168,20 @@ def backbone_forward(sd, z_img, x_img, ce_template_mask, prompt_type="vipt_deep"
         y, attn = _attention(_ln(x, sd, blk + ".norm1"), sd, blk + ".attn")
         x = x + y
         if i in CE_LOC:
-            x, gi_s, rem, score = _candidate_elimination(attn, x, lens_z, CE_KEEP, gi_s, ce_template_mask)
+            ce_index.append(gi_s)
+            x, gi_s, rem, score = _candidate_elimination(
+                attn, x, lens_z, CE_KEEP, gi_s, ce_template_mask,
+                None if forced_removed is None else forced_removed[len(removed)])     # entries may be None
             removed.append(rem)
             ce_scores.append(score)
-        h = F.linear(_ln(x, sd, blk + ".norm2"), sd[blk + ".mlp.fc1.weight"], sd[blk + ".mlp.fc1.bias"])
-        h = F.gelu(h)                                              # exact erf
-        x = x + F.linear(h, sd[blk + ".mlp.fc2.weight"], sd[blk + ".mlp.fc2.bias"])
+        h = F.linear(_q(_ln(x, sd, blk + ".norm2")), _q(sd[blk + ".mlp.fc1.weight"]), sd[blk + ".mlp.fc1.bias"])
+        h = _q(F.gelu(h))                                          # exact erf
+        x = x + _q(F.linear(h, _q(sd[blk + ".mlp.fc2.weight"]), sd[blk + ".mlp.fc2.bias"]))
     x = _ln(x, sd, bb + "norm")
     full_s = _scatter_full(x[:, lens_z:], gi_s, removed, lens_x)     # exact zeros at removed positions
     feat = torch.cat([x[:, :lens_z], full_s], dim=1)
-    aux = {"attn": attn, "removed_indexes_s": removed, "ce_scores": ce_scores, "global_index_s": gi_s}
+    aux = {"attn": attn, "removed_indexes_s": removed, "ce_scores": ce_scores, "ce_index": ce_index,
+           "global_index_s": gi_s}
     return feat, aux
 
 
@@ -196,9 +219,9 @@ def cal_bbox(score_map, size_map, offset_map):
     return bbox, max_score
 
 
-def model_forward(sd, template, search, ce_template_mask, prompt_type="vipt_deep", trace=None):
+def model_forward(sd, template, search, ce_template_mask, prompt_type="vipt_deep", trace=None, forced_removed=None):
     """ViPTrack.forward (ostrack_prompt.py:39-58): same dict keys."""
-    feat, aux = backbone_forward(sd, template, search, ce_template_mask, prompt_type, trace)
+    feat, aux = backbone_forward(sd, template, search, ce_template_mask, prompt_type, trace, forced_removed)
     score, size, offset = head_forward(sd, feat)
     bbox, _ = cal_bbox(score, size, offset)
     out = {"pred_boxes": bbox.view(-1, 1, 4), "score_map": score, "size_map": size, "offset_map": offset,

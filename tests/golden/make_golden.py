@@ -7,6 +7,8 @@ Needs /root/reference (see oracle/ref_harness.py); the GPU box never runs this. 
   tests/golden/model_golden.npz   build_viptrack(...).forward on seeded inputs (deep + shaw)
   tests/golden/track_golden.npz   ViPTTrack.initialize/track over seeded synthetic sequences
   tests/golden/frames_golden.npz  get_x_frame ('rgbrgb', 'rgbcolormap' with / without depth clip) on synthetic PNGs
+  tests/golden/peaked_golden.npz  the "peaked" weight set (synth.WEIGHT_SETS): model forward (deep + shaw) and the
+                                  50-frame deep-RGBD tracking run of BASELINE.json configs[0]  (--peaked-only)
 Weights are not stored: vipt_b200.synth.synthetic_state_dict(seed) regenerates them.
 """
 import os
@@ -93,6 +95,41 @@ def track_golden():
     np.savez_compressed(os.path.join(OUT, "track_golden.npz"), **out)
 
 
+def peaked_golden():
+    """Same two generators on the peaked-attention weight set; the tracking run is BASELINE.json configs[0]:
+    one DepthTrack-shaped sequence, 50 tracked frames, batch 1 (sequence seed 300 = sequence 0 of
+    oracle/parity_run.py)."""
+    out = {}
+    for name, yaml_name, ptype in (("deep", "deep_rgbt", "vipt_deep"), ("shaw", "shaw_rgbd", "vipt_shaw")):
+        sd = synth.weight_set("peaked", ptype)
+        model, cfg = rh.build_reference_model(yaml_name)
+        model.load_state_dict(sd, strict=True)
+        g = torch.Generator().manual_seed(321)
+        z = torch.randn(4, 6, 128, 128, generator=g); x = torch.randn(4, 6, 256, 256, generator=g)
+        from lib.utils.ce_utils import generate_mask_cond
+        mask = generate_mask_cond(cfg, 4, z.device, None)
+        with torch.no_grad():
+            o = model(template=z, search=x, ce_template_mask=mask)
+        for k in ("pred_boxes", "score_map", "size_map", "offset_map"):
+            out[name + "_" + k] = o[k].numpy()
+        out[name + "_feat_sample"] = o["backbone_feat"][:, ::16, ::32].numpy()
+        for i, r in enumerate(o["removed_indexes_s"]):
+            out[name + "_removed_%d" % i] = r.numpy()
+        out[name + "_attn_row27"] = o["attn"][:, :, 27, :].numpy()
+    T = 51
+    sd = synth.weight_set("peaked", "vipt_deep")
+    tr = rh.make_tracker("deep_rgbd", sd)
+    frames, box0, _ = synth.synthetic_sequence(300, T, "rgbd")
+    tr.initialize(frames[0], {"init_bbox": list(box0)})
+    boxes = [list(box0)]; scores = [1.0]
+    for t in range(1, T):
+        r = tr.track(frames[t])
+        boxes.append(list(r["target_bbox"])); scores.append(r["best_score"])
+    out["track_seed"] = np.int64(300); out["track_T"] = np.int64(T)
+    out["track_boxes"] = np.array(boxes, np.float64); out["track_scores"] = np.array(scores, np.float64)
+    np.savez_compressed(os.path.join(OUT, "peaked_golden.npz"), **out)
+
+
 def frames_golden():
     """get_x_frame (ViPT/lib/train/dataset/depth_utils.py:70-132) on small synthetic image files."""
     import tempfile
@@ -131,6 +168,10 @@ if __name__ == "__main__":
         frames_golden()
         sys.exit(0)
     torch.set_num_threads(8)
+    if "--peaked-only" in sys.argv:
+        peaked_golden()
+        sys.exit(0)
+    peaked_golden()
     crop_golden(); model_golden(); track_golden(); frames_golden()
     for f in ("crop_golden.npz", "model_golden.npz", "track_golden.npz"):
         print(f, os.path.getsize(os.path.join(OUT, f)))
