@@ -19,7 +19,11 @@ import tempfile
 
 import torch
 
-REF_ROOT = os.environ.get("VIPT_REFERENCE_ROOT", "/root/reference/ViPT")
+# the checkout in the build container, else the byte-for-byte copy of the path's files that oracle/make_ref.py put
+# under oracle/_ref (git-ignored; travels to the GPU box with the snapshot)
+_TRAVEL = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "ViPT")
+REF_ROOT = os.environ.get("VIPT_REFERENCE_ROOT") or (
+    "/root/reference/ViPT" if os.path.isdir("/root/reference/ViPT/lib") else _TRAVEL)
 _STUBS = os.path.join(os.path.dirname(os.path.abspath(__file__)), "stubs")
 
 

@@ -123,7 +123,7 @@ def _scatter_full(x_s, global_index_s, removed, lens_x):
     if not removed:
         return x_s
     removed_cat = torch.cat(removed, dim=1)
-    pad = torch.zeros(B, lens_x - x_s.shape[1], C)
+    pad = torch.zeros(B, lens_x - x_s.shape[1], C, dtype=x_s.dtype, device=x_s.device)
     x_s = torch.cat([x_s, pad], dim=1)
     index_all = torch.cat([global_index_s, removed_cat], dim=1)
     return torch.zeros_like(x_s).scatter_(1, index_all.unsqueeze(-1).expand(B, -1, C), x_s)
@@ -145,7 +145,7 @@ def backbone_forward(sd, z_img, x_img, ce_template_mask, prompt_type="vipt_deep"
     x = x + x_prompted + sd[bb + "pos_embed_x"]
     lens_z, lens_x = z.shape[1], x.shape[1]
     x = torch.cat([z, x], dim=1)                                   # cat_mode 'direct'
-    gi_s = torch.arange(lens_x, dtype=torch.int64).repeat(B, 1)
+    gi_s = torch.arange(lens_x, dtype=torch.int64, device=x.device).repeat(B, 1)
     removed = []
     ce_scores = []
     ce_index = []          # raster position of every search slot entering each CE stage (ce_scores column order)
