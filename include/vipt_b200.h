@@ -44,6 +44,22 @@ int vipt_op_crop(const void* frame_ptrs_dev, const int* hw_dev, const double* bo
  * (ViPT/lib/models/layers/attn.py:33-59, attn_blocks.py:44-53). */
 int vipt_op_attention(const void* qkv, int B, int N, void* out, float* ce_prob, void* stream);
 
+/* Candidate-elimination ranking (ViPT/lib/models/layers/attn_blocks.py:37-63): score[j] = mean over heads of
+ * ce_prob (B, n_heads, 256)[.., j], j < n_s; descending order, exact ties keep the LOWER slot first (torch.sort is
+ * not stable, so the reference leaves the order of exact ties unspecified).  gi_in/gi_out (B,256): raster position
+ * of each slot before / after; perm (B,256): old slot of new slot r; removed (B,256): raster positions of the dropped
+ * tokens in score order; slot_of_pos (B,256): new slot of a raster position or -1; score_out (B,256) or NULL. */
+int vipt_op_ce_topk(const float* ce_prob, int n_heads, int n_s, int n_keep, const int* gi_in, int* gi_out, int* perm,
+                    int* removed, int* slot_of_pos, float* score_out, int B, void* stream);
+
+/* 3x3 convolution, padding 1, + bias + ReLU over a (B,16,16,c_total) fp16 feature map as an implicit GEMM (the
+ * conv + folded BatchNorm + ReLU of ViPT/lib/models/layers/head.py:8-21).  Group g reads channels
+ * [g*cin_stride, +cin) and writes columns [g*out_group_col, +N) of out (B*256, ldc) fp16; W (G, N, 9*cin) fp16 with
+ * K order tap*cin + c, tap = ky*3 + kx; bias (G, N).  bn: N-tile of the single-CTA kernel (32..256), or 512 for the
+ * 2-CTA kernel (G = 1, N % 256 == 0). */
+int vipt_op_conv3x3(const void* feat, int c_total, int cin, int cin_stride, const void* W, int G, int B, int N, int bn,
+                    void* out, int64_t ldc, int64_t out_group_col, const float* bias, void* stream);
+
 /* Frame assembly after image decode (get_x_frame / get_rgbd_frame, ViPT/lib/train/dataset/depth_utils.py:7-132).
  * rgbx: dtype 'rgbrgb' -- two BGR uint8 (H,W,3) images -> RGB||RGB uint8 (H,W,6).
  * rgbd: dtype 'rgbcolormap' -- BGR uint8 (H,W,3) + uint16 depth (H,W): optional clip at min(3*median, 10000),

@@ -22,6 +22,10 @@ SIGNATURES = {
     "vipt_op_crop": (c_int, [c_void_p, c_void_p, c_void_p, c_double, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                              c_int, c_void_p]),
     "vipt_op_attention": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "vipt_op_ce_topk": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                c_int, c_void_p]),
+    "vipt_op_conv3x3": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_i64,
+                                c_i64, c_void_p, c_void_p]),
     "vipt_op_assemble_rgbx": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),
     "vipt_op_assemble_rgbd": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "vipt_engine_create": (c_int, [ctypes.POINTER(c_void_p)]),

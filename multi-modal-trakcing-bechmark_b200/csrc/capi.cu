@@ -47,6 +47,25 @@ int vipt_op_attention(const void* qkv, int B, int N, void* out, float* ce_prob, 
   return vipt::attention_launch(op, out, ce_prob, vipt::kCeToken, vipt::kLensT, vipt::kLensX, (cudaStream_t)stream);
 }
 
+int vipt_op_ce_topk(const float* ce_prob, int n_heads, int n_s, int n_keep, const int* gi_in, int* gi_out, int* perm,
+                    int* removed, int* slot_of_pos, float* score_out, int B, void* stream) {
+  if (!ce_prob || !gi_in || !gi_out || !perm || !removed || !slot_of_pos || n_keep < 1 || n_keep > n_s) return VIPT_ERR_ARG;
+  return vipt::launch_ce_topk(ce_prob, n_heads, n_s, n_keep, gi_in, gi_out, perm, removed, slot_of_pos, score_out,
+                              vipt::kLensX, B, (cudaStream_t)stream);
+}
+
+int vipt_op_conv3x3(const void* feat, int c_total, int cin, int cin_stride, const void* W, int G, int B, int N, int bn,
+                    void* out, int64_t ldc, int64_t out_group_col, const float* bias, void* stream) {
+  vipt::GemmOp op;
+  int r = bn == 512 ? vipt::gemm2_plan_conv(&op, feat, c_total, cin, W, B, N, vipt::EPI_RELU_F16, out, ldc, bias)
+                    : vipt::gemm_plan_conv(&op, feat, c_total, cin, cin_stride, W, G, B, N, bn, vipt::EPI_RELU_F16, out, ldc,
+                                           out_group_col, bias);
+  if (r) { set_err("conv plan failed"); return r; }
+  r = vipt::gemm_launch(op, num_sms(), (cudaStream_t)stream);
+  if (r) set_err(cudaGetErrorString(cudaGetLastError()));
+  return r;
+}
+
 int vipt_op_assemble_rgbx(const void* bgr_dev, const void* xbgr_dev, int H, int W, void* out_dev, void* stream) {
   if (!bgr_dev || !xbgr_dev || !out_dev || H < 1 || W < 1) return VIPT_ERR_ARG;
   return vipt::launch_assemble_rgbx(bgr_dev, xbgr_dev, H, W, out_dev, (cudaStream_t)stream);

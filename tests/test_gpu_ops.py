@@ -91,3 +91,76 @@ def test_attention(B, N):
         ce_ref = p[:, :, 27, 64:]
         ce_err = (ce[:, :, :N - 64] - ce_ref).abs().max().item()
         assert ce_err < 1e-5 + 1e-4 * ce_ref.max().item(), ce_err
+
+
+@pytest.mark.parametrize("n_s,n_keep", [(256, 180), (180, 126), (126, 89)])
+def test_ce_topk_against_reference_sort(n_s, n_keep):
+    """ce_topk_kernel against attn_blocks.py:37-63 (mean over heads, descending sort, keep ceil(0.7 n)): index work,
+    bit-exact.  Sequence 0 has distinct scores (the order must equal torch.sort's); sequence 1 contains groups of EXACT
+    ties, across the keep boundary too: there the reference's order is unspecified (torch.sort is not stable) and the
+    documented rule of this implementation is 'lower slot first' = a stable descending sort."""
+    L = _lib.lib()
+    dev = torch.device("cuda")
+    B, H = 3, 12
+    g = torch.Generator().manual_seed(n_s)
+    prob = torch.rand(B, H, 256, generator=g)
+    prob[1] = torch.randint(0, 6, (1, 256), generator=g).float().expand(H, 256) / 8.0       # many exact ties
+    prob[2, :, n_keep - 2:n_keep + 3] = 0.5                                                   # a tie across the boundary
+    gi_in = torch.stack([torch.randperm(256, generator=g) for _ in range(B)]).int()
+    ce = prob.to(dev)
+    gi_out = torch.full((B, 256), -7, dtype=torch.int32, device=dev)
+    perm = torch.full((B, 256), -7, dtype=torch.int32, device=dev)
+    removed = torch.full((B, 256), -7, dtype=torch.int32, device=dev)
+    sop = torch.full((B, 256), -7, dtype=torch.int32, device=dev)
+    score = torch.zeros(B, 256, device=dev)
+    _lib.check(L.vipt_op_ce_topk(_lib.ptr(ce), H, n_s, n_keep, _lib.ptr(gi_in.to(dev)), _lib.ptr(gi_out), _lib.ptr(perm),
+                                 _lib.ptr(removed), _lib.ptr(sop), _lib.ptr(score), B, _lib.stream_ptr()), "ce_topk")
+    torch.cuda.synchronize()
+    ref_score = prob[:, :, :n_s].mean(dim=1)
+    # the device sums the heads in order and divides by 12: same value as torch's mean up to fp32 summation order
+    np.testing.assert_allclose(score.cpu()[:, :n_s].numpy(), ref_score.numpy(), rtol=2e-6)
+    dscore = score.cpu()[:, :n_s]
+    order = torch.sort(dscore, dim=1, descending=True, stable=True).indices          # documented tie rule
+    for b in range(B):
+        keep, drop = order[b, :n_keep], order[b, n_keep:]
+        assert torch.equal(perm[b, :n_keep].cpu().long(), keep)
+        assert torch.equal(gi_out[b, :n_keep].cpu().long(), gi_in[b].long()[keep])
+        assert torch.equal(removed[b, :n_s - n_keep].cpu().long(), gi_in[b].long()[drop])
+        s = sop[b].cpu().long()
+        assert torch.equal(s[gi_in[b].long()[keep]], torch.arange(n_keep))
+        assert (s[gi_in[b].long()[drop]] == -1).all()
+    # distinct scores: exactly the reference's (unstable) sort
+    ref_order = torch.sort(ref_score[0], descending=True).indices
+    if torch.equal(dscore[0], ref_score[0]):
+        assert torch.equal(perm[0, :n_keep].cpu().long(), ref_order[:n_keep])
+
+
+@pytest.mark.parametrize("B,cin,N,G,bn", [
+    (64, 768, 768, 1, 512),      # head conv1, three towers concatenated on N, 2-CTA kernel (large batch)
+    (2, 768, 768, 1, 64),        # head conv1 in latency mode (single-CTA, narrow tiles)
+    (5, 256, 128, 3, 128),       # conv2: three towers as groups reading their own 256 channels
+    (5, 128, 64, 3, 64),         # conv3
+    (3, 64, 32, 3, 32),          # conv4
+])
+def test_implicit_conv3x3_against_conv2d(B, cin, N, G, bn):
+    """The implicit-GEMM 3x3 convolution (4-D TMA map, zero padding by out-of-bounds fill, bias + ReLU fused) against
+    torch conv2d in fp32 on the same fp16-rounded operands (ViPT/lib/models/layers/head.py:8-21 with BN folded)."""
+    L = _lib.lib()
+    dev = torch.device("cuda")
+    g = torch.Generator().manual_seed(B * 1000 + cin)
+    c_total = cin * G
+    feat = (torch.randn(B, 16, 16, c_total, generator=g) * 0.7).half()
+    w = (torch.randn(G, N, cin, 3, 3, generator=g) / np.sqrt(9 * cin)).half()
+    bias = torch.randn(G, N, generator=g) * 0.1
+    wk = w.permute(0, 1, 3, 4, 2).reshape(G, N, 9 * cin).contiguous()               # K order tap * cin + c
+    out = torch.full((B * 256, G * N), float("nan"), dtype=torch.float16, device=dev)
+    _lib.check(L.vipt_op_conv3x3(_lib.ptr(feat.to(dev)), c_total, cin, cin, _lib.ptr(wk.to(dev)), G, B, N, bn,
+                                 _lib.ptr(out), G * N, N, _lib.ptr(bias.to(dev)), _lib.stream_ptr()), "conv3x3")
+    torch.cuda.synchronize()
+    x = feat.float().permute(0, 3, 1, 2)
+    for gg in range(G):
+        ref = torch.relu(torch.nn.functional.conv2d(x[:, gg * cin:(gg + 1) * cin], w[gg].float(), bias[gg], padding=1))
+        ref = ref.permute(0, 2, 3, 1).reshape(B * 256, N)
+        got = out[:, gg * N:(gg + 1) * N].float().cpu()
+        err = (got - ref).abs().max().item() / ref.abs().max().item()
+        assert err < 2e-3, (gg, err)
