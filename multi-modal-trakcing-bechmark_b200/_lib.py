@@ -4,6 +4,7 @@ import os
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_PKG, "libvipt_b200.so")
+_EXPERIMENT = os.environ.get("VIPT_EXPERIMENT_LIB")     # kernel experiments only (scripts/): another build of the library
 
 _lib = None
 
@@ -56,7 +57,7 @@ def lib():
         if not os.path.exists(LIB_PATH):
             raise ViptError("libvipt_b200.so is not built (%s); run `python __graft_entry__.py build` -- "
                             "there is no CPU fallback" % LIB_PATH)
-        L = ctypes.CDLL(LIB_PATH)
+        L = ctypes.CDLL(_EXPERIMENT if _EXPERIMENT else LIB_PATH)
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(L, name)
             fn.restype = res

@@ -219,7 +219,8 @@ int attention_launch(const AttnOp& op, void* out, float* ce_prob, int ce_row, in
   // 128-query tile keeps more SMs busy
   if (op.N > kQTile && op.B * 12 >= num_sms && !getenv("VIPT_ATTENTION_V1")) {
     if (getenv("VIPT_ATTENTION_V2")) return attention2_launch(op, out, ce_prob, ce_row, lens_t, ce_stride, num_sms, st);
-    return attention3_launch(op, out, ce_prob, ce_row, lens_t, ce_stride, num_sms, st);
+    if (getenv("VIPT_ATTENTION_V3")) return attention3_launch(op, out, ce_prob, ce_row, lens_t, ce_stride, num_sms, st);
+    return attention4_launch(op, out, ce_prob, ce_row, lens_t, ce_stride, num_sms, st);
   }
   dim3 grid((op.N + kQTile - 1) / kQTile, 12, op.B);
   const float scale_log2 = 0.125f * 1.4426950408889634f;

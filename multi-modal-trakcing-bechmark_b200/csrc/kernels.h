@@ -50,6 +50,9 @@ int attention2_launch(const AttnOp& op, void* out, float* ce_prob, int ce_row, i
 int attention3_launch(const AttnOp& op, void* out, float* ce_prob, int ce_row, int lens_t, int ce_stride, int num_sms,
                       cudaStream_t st);    // same, score MMAs running ahead of the softmax (attention3.cu)
 
+int attention4_launch(const AttnOp& op, void* out, float* ce_prob, int ce_row, int lens_t, int ce_stride, int num_sms,
+                      cudaStream_t st);    // 16 softmax warps, two threads per row, rotating K / V slots (attention4.cu)
+
 int launch_head_final(const void* h4, const float* w5, const float* b5, const float* window, float* score_map,
                       float* size_map, float* offset_map, float* pred_boxes, double* state, const double* geom,
                       const int* frame_hw, double* out_boxes, float* out_scores, int B, cudaStream_t st);

@@ -113,7 +113,8 @@ def test_ce_topk_against_reference_sort(n_s, n_keep):
     removed = torch.full((B, 256), -7, dtype=torch.int32, device=dev)
     sop = torch.full((B, 256), -7, dtype=torch.int32, device=dev)
     score = torch.zeros(B, 256, device=dev)
-    _lib.check(L.vipt_op_ce_topk(_lib.ptr(ce), H, n_s, n_keep, _lib.ptr(gi_in.to(dev)), _lib.ptr(gi_out), _lib.ptr(perm),
+    gi_in_d = gi_in.to(dev)
+    _lib.check(L.vipt_op_ce_topk(_lib.ptr(ce), H, n_s, n_keep, _lib.ptr(gi_in_d), _lib.ptr(gi_out), _lib.ptr(perm),
                                  _lib.ptr(removed), _lib.ptr(sop), _lib.ptr(score), B, _lib.stream_ptr()), "ce_topk")
     torch.cuda.synchronize()
     ref_score = prob[:, :, :n_s].mean(dim=1)
@@ -154,8 +155,9 @@ def test_implicit_conv3x3_against_conv2d(B, cin, N, G, bn):
     bias = torch.randn(G, N, generator=g) * 0.1
     wk = w.permute(0, 1, 3, 4, 2).reshape(G, N, 9 * cin).contiguous()               # K order tap * cin + c
     out = torch.full((B * 256, G * N), float("nan"), dtype=torch.float16, device=dev)
-    _lib.check(L.vipt_op_conv3x3(_lib.ptr(feat.to(dev)), c_total, cin, cin, _lib.ptr(wk.to(dev)), G, B, N, bn,
-                                 _lib.ptr(out), G * N, N, _lib.ptr(bias.to(dev)), _lib.stream_ptr()), "conv3x3")
+    feat_d, wk_d, bias_d = feat.to(dev), wk.to(dev), bias.to(dev)       # named: they must outlive the launch
+    _lib.check(L.vipt_op_conv3x3(_lib.ptr(feat_d), c_total, cin, cin, _lib.ptr(wk_d), G, B, N, bn,
+                                 _lib.ptr(out), G * N, N, _lib.ptr(bias_d), _lib.stream_ptr()), "conv3x3")
     torch.cuda.synchronize()
     x = feat.float().permute(0, 3, 1, 2)
     for gg in range(G):
