@@ -217,11 +217,7 @@ int attention_launch(const AttnOp& op, void* out, float* ce_prob, int ce_row, in
   }
   // the persistent kernel needs >= one (sequence, head) item per SM to pay off; below that (latency mode) one CTA per
   // 128-query tile keeps more SMs busy
-  if (op.N > kQTile && op.B * 12 >= num_sms && !getenv("VIPT_ATTENTION_V1")) {
-    if (getenv("VIPT_ATTENTION_V2")) return attention2_launch(op, out, ce_prob, ce_row, lens_t, ce_stride, num_sms, st);
-    if (getenv("VIPT_ATTENTION_V3")) return attention3_launch(op, out, ce_prob, ce_row, lens_t, ce_stride, num_sms, st);
-    return attention4_launch(op, out, ce_prob, ce_row, lens_t, ce_stride, num_sms, st);
-  }
+  if (op.N > kQTile && op.B * 12 >= num_sms) return attention4_launch(op, out, ce_prob, ce_row, lens_t, ce_stride, num_sms, st);
   dim3 grid((op.N + kQTile - 1) / kQTile, 12, op.B);
   const float scale_log2 = 0.125f * 1.4426950408889634f;
   const int smem = att_smem_bytes(op.nkp);

@@ -1,9 +1,10 @@
 // Persistent, warp-specialised joint template+search attention (ViPT/lib/models/layers/attn.py:33-59) for N > 128
-// tokens, fourth generation.  Same dataflow as attention3.cu (one CTA per SM walks a contiguous range of
-// (sequence, head, 128-query tile) units; keys of a tile in <= 3 chunks of <= 128; S_k = Q K_k^T runs up to three
-// chunks ahead in TMEM; P_k through swizzled smem; O_k = P_k V_k drained per chunk into an online softmax held in
-// the epilogue warps' registers), rebuilt around what the round-2 measurements of attention3 showed
-// (profiles/r2_attention3_trace.txt, r2_attention3_ablation.txt, r2_ubench_softmax.txt):
+// tokens.  One CTA per SM walks a contiguous range of (sequence, head, 128-query tile) units; the keys of a tile are
+// cut into <= 3 chunks of <= 128, and the chunks of all tiles form one stream k = 0, 1, 2, ...: S_k = Q K_k^T runs up
+// to three chunks ahead of the softmax in TMEM; P_k goes through swizzled shared memory; O_k = P_k V_k is drained per
+// chunk into an online softmax held in the epilogue warps' registers (TMEM accumulators are never rescaled).
+// Built around what the round-2 measurements of its round-1 predecessor showed (profiles/r2_attention3_trace.txt,
+// r2_attention3_ablation.txt, r2_ubench_softmax.txt):
 //
 //   * the softmax warps ran at half the rate the same loop reaches in isolation (6.7 vs 13.7 elements/clk/SM with
 //     8 warps): 16 softmax warps now, TWO threads per query row (warps w and w+4 of a group own the same TMEM lane

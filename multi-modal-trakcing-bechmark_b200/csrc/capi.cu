@@ -79,7 +79,10 @@ int vipt_op_assemble_rgbd(const void* bgr_dev, const void* depth16_dev, int H, i
 // ---------------------------------------------------------------- engine
 int vipt_engine_create(void** out) {
   if (!out) return VIPT_ERR_ARG;
-  *out = new vipt::Engine();
+  vipt::Engine* e = new vipt::Engine();
+  e->opt_zero_copy = getenv("VIPT_NO_ZEROCOPY") == nullptr;
+  e->opt_speculate = getenv("VIPT_NO_SPECULATION") == nullptr;
+  *out = e;
   return VIPT_OK;
 }
 int vipt_engine_destroy(void* e) {

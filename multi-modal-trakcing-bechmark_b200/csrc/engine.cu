@@ -191,7 +191,7 @@ int Engine::finalize(int batch, bool deep_prompt) {
     PW[i].smooth = (*pk.get(p + "fovea.smooth", 1))[0];
     PW[i].fold = nullptr; PW[i].w1t = nullptr;
     if (i >= 1) {
-      // fused deep-prompt kernel (prompt_fused.cu): conv1x1 transposed to k-major, and the previous
+      // fused deep-prompt kernel (prompt_coop.cu): conv1x1 transposed to k-major, and the previous
       // prompt P = W1p f + b1p (rank 8) folded through prompt_norms[i] and conv0_1 of this block.
       const auto& w1 = *pk.get(p + "conv1x1.weight", 768 * 8);
       std::vector<float> w1t(8 * 768);

@@ -86,6 +86,10 @@ struct Engine {
   std::vector<int> host_hw;
   std::vector<double> host_state;
   bool mirror_valid = false;
+  // host-frame path switches, read ONCE from the environment when the engine is created:
+  // VIPT_NO_ZEROCOPY=1 uploads page-locked frames with per-sequence 2-D copies instead of the gather kernel,
+  // VIPT_NO_SPECULATION=1 disables the copy-engine upload next to the running step.  Both covered by tests.
+  bool opt_zero_copy = true, opt_speculate = true;
   // zero-copy gather: the device-visible addresses of the B host frames travel as a kernel parameter
   static constexpr int kRoiSlots = 4;      // steps that may be enqueued before their results are collected
   static constexpr int kRoiMaxB = 128;

@@ -100,15 +100,12 @@ int Engine::finalize_buffers() {
     if (pair_tiles >= num_sms / 2) return gemm2_plan(op, A, lda, W, K, M, N, K, epi, out, N, bias, num_sms / 2);
     const int mt = (M + 127) / 128;
     int bn = 128;
-    static const bool old_policy = getenv("VIPT_BN_POLICY_OLD") != nullptr;
-    if (old_policy) {
-      while (bn > 32 && mt * (N / bn) < num_sms) bn >>= 1;
-    } else {
+    {
       // These GEMMs are bound by the operand stream into each SM ((128 + bn) x 64 fp16 per k-block), not by the MMAs:
       // pick the tile width that minimises  rounds x (128 + bn), ties to the wider tile (less total L2 traffic).
       // E.g. one sequence (3 row tiles): qkv 108 x bn64 tiles in one round instead of 216 x bn32 in two.  Measured
       // against the previous rule (narrowest tile that still gives >= #SMs tiles): step 0.848 -> 0.828 ms at one
-      // sequence, 1.058 -> 0.979 at 4, 1.297 -> 1.181 at 8, 1.628 -> 1.574 at 16 (VIPT_BN_POLICY_OLD=1 restores it).
+      // sequence, 1.058 -> 0.979 at 4, 1.297 -> 1.181 at 8, 1.628 -> 1.574 at 16.
       int best = 1 << 30;
       for (int c = 128; c >= 32; c >>= 1) {
         const int tiles = mt * (N / c), rounds = (tiles + num_sms - 1) / num_sms, cost = rounds * (128 + c);
@@ -156,7 +153,6 @@ int Engine::run_backbone_head(bool tracking, bool want_feat32, int debug_stop, c
   long nl = 0;
   int stage = 0;
   pdl_select(B, num_sms);
-  static const bool use_cluster_prompt = getenv("VIPT_PROMPT_CLUSTER") != nullptr;
 #define LAUNCH(cls, expr)   \
   do {                      \
     prof_begin(cls, st);    \
@@ -195,13 +191,9 @@ int Engine::run_backbone_head(bool tracking, bool want_feat32, int debug_stop, c
     const int n = n_tok[i];
     if (i >= 1) {
       if (deep) {
-        // cooperative persistent kernel (prompt_coop.cu); the cluster kernel (prompt_fused.cu) stays selectable
-        if (use_cluster_prompt)
-          LAUNCH(K_PROMPT, launch_prompt_fused(x, dbuf, n, gi, FV, PW[i].wg_a, PW[i].fold, PW[i].w1t, PW[i].b1, L[i].ln1_g,
-                                               L[i].ln1_b, xn, B, kLensT, kLensFull, st));
-        else
-          LAUNCH(K_PROMPT, launch_prompt_coop(x, dbuf, n, gi, FV, XD, PW[i].wg_a, PW[i].fold, PW[i].w1t, PW[i].b1,
-                                              L[i].ln1_g, L[i].ln1_b, xn, B, kLensT, kLensFull, num_sms, st));
+        // cooperative persistent kernel (prompt_coop.cu)
+        LAUNCH(K_PROMPT, launch_prompt_coop(x, dbuf, n, gi, FV, XD, PW[i].wg_a, PW[i].fold, PW[i].w1t, PW[i].b1,
+                                            L[i].ln1_g, L[i].ln1_b, xn, B, kLensT, kLensFull, num_sms, st));
       } else {
         LAUNCH(K_NORM, launch_ln_rows(x, n, dbuf, nullptr, 0, x, xn, L[i].ln1_g, L[i].ln1_b, B, n, kLensT, st));
       }

@@ -169,7 +169,7 @@ int Engine::track_host(const void* const* host_frames, bool use_graph, int64_t* 
   int64_t total = 0;
   long long spec_total = 0;
   // zero-copy gather when every frame is page-locked and device-visible
-  bool mapped = getenv("VIPT_NO_ZEROCOPY") == nullptr;
+  bool mapped = opt_zero_copy;
   std::vector<const uint8_t*> dev_src(B, nullptr);
   for (int b = 0; mapped && b < B; ++b) {
     cudaPointerAttributes at;
@@ -188,7 +188,7 @@ int Engine::track_host(const void* const* host_frames, bool use_graph, int64_t* 
     for (int b = 0; b < B; ++b) srcs.p[b] = dev_src[b];
     uint8_t* const* dst_tab = own_tab_dev + (size_t)set * B;
     int* rb = roi_bytes_dev + (size_t)set * 2 * B;
-    const bool speculate = res_pending > 0 && (int)spec_state.size() == 4 * B && getenv("VIPT_NO_SPECULATION") == nullptr;
+    const bool speculate = res_pending > 0 && (int)spec_state.size() == 4 * B && opt_speculate;
     long long spec_bytes = 0;
     if (speculate) {
       // A step is in flight and its boxes are not known yet: while it runs, the copy engine uploads -- on a side

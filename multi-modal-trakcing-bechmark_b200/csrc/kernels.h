@@ -23,9 +23,6 @@ int launch_fovea(const float* xd, float smooth, float* F, int B, int lens_t, int
 int launch_prompt_b(const float* F, const float* w1, const float* b1, float* P, const float* base, const void* delta,
                     float* x, int n_cur, const int* slot_of_pos, const float* pos_embed, const float* gamma1,
                     const float* beta1, void* xn, int B, int lens_t, int lens_full, cudaStream_t st);
-int launch_prompt_fused(float* x, const void* delta, int n_cur, const int* gi, float* F, const float* wg_a,
-                        const float* fold, const float* w1t, const float* b1, const float* gamma1, const float* beta1,
-                        void* xn, int B, int lens_t, int lens_full, cudaStream_t st);
 int launch_prompt_coop(float* x, const void* delta, int n_cur, const int* gi, float* F, float* X0, const float* wg_a,
                        const float* fold, const float* w1t, const float* b1, const float* gamma1, const float* beta1,
                        void* xn, int B, int lens_t, int lens_full, int num_sms, cudaStream_t st);
@@ -44,12 +41,7 @@ struct AttnOp {
 };
 int attention_plan(AttnOp* op, const void* qkv, int B, int N);
 int attention_launch(const AttnOp& op, void* out, float* ce_prob, int ce_row, int lens_t, int ce_stride,
-                     cudaStream_t st);     // N <= 128: one CTA per (sequence, head); else dispatches to attention2
-int attention2_launch(const AttnOp& op, void* out, float* ce_prob, int ce_row, int lens_t, int ce_stride, int num_sms,
-                      cudaStream_t st);    // persistent warp-specialised kernel (attention2.cu), N > 128
-int attention3_launch(const AttnOp& op, void* out, float* ce_prob, int ce_row, int lens_t, int ce_stride, int num_sms,
-                      cudaStream_t st);    // same, score MMAs running ahead of the softmax (attention3.cu)
-
+                     cudaStream_t st);     // one CTA per (sequence, head, tile) in latency mode, else attention4
 int attention4_launch(const AttnOp& op, void* out, float* ce_prob, int ce_row, int lens_t, int ce_stride, int num_sms,
                       cudaStream_t st);    // 16 softmax warps, two threads per row, rotating K / V slots (attention4.cu)
 

@@ -1,5 +1,18 @@
 // Deep-prompt stage of layers 1..11 (ViPT/lib/models/vipt/vit_ce_prompt.py:268-310) as ONE cooperative,
-// persistent kernel with a single grid-wide barrier (same mathematics as prompt_fused.cu, see there):
+// persistent kernel with a single grid-wide barrier:
+//   x      <- x + delta                       (delta = fp16 output of the previous block's mlp.fc2)
+//   x0     = conv0_0(prompt_norms[i-1](x))     per kept token          (Prompt_block, :63-65)
+//   x1     = conv0_1(prompt_norms[i](P_prev))  per kept position       (:66)
+//   F      = softmax_over_positions(smooth * x0) * x0 + x1             (Fovea, :37-47)
+//   x      <- x + conv1x1(F)                   kept positions, current token order (:308-310)
+//   xn     = blocks[i].norm1(x) in fp16        feeds the qkv GEMM      (attn_blocks.py:94)
+//
+// The prompt stream itself is never materialised.  P_prev = conv1x1_{i-1}(F_prev) has rank 8, so
+//   conv0_1(LN(P_prev[t])) = (A f + a0) * rstd(f) + c_d,  var(f) = f^T G f + 2 h.f + c0,  f = F_prev[t]
+// with 8x8 / 8-vectors folded once on the host in double (engine.cu); only F (8 floats per position)
+// travels between layers.  Removed search positions are zero rows before prompt_norms[i-1]
+// (:276-288), i.e. x0 = conv0_0(beta) = c_a there: they enter the softmax normaliser as
+// n_removed * exp(smooth * c_a - max) and nothing else depends on them.
 //
 //   phase 1  every warp streams token rows (two at a time): v = x + delta, LayerNorm statistics and the
 //            768 -> 8 down-projection x0 = conv0_0(prompt_norms[i-1](v)); x0 goes to a small global array
@@ -9,9 +22,10 @@
 //            SM's neighbours), forms F = softmax * x0 + x1 (x1 from the previous layer's F by the rank-8
 //            algebra), adds the 8 -> 768 up-projection, writes x and xn = blocks[i].norm1(x) in fp16.
 //
-// The cluster version keeps rows in registers across a cluster barrier, which costs it occupancy (one CTA
-// per SM) and serialises load / math / barrier / math / store inside every CTA.  Here nothing is held
-// across the barrier: 16 warps per SM stream independently, DRAM reads happen once (phase 2 hits L2).
+// Nothing is held across the barrier: 16 warps per SM stream independently, DRAM reads happen once (phase 2 hits
+// L2).  (A round-1 variant with a cluster of 8 CTAs per sequence kept the rows in registers across a cluster barrier
+// and exchanged the softmax statistics through distributed shared memory; it was limited to one CTA per SM and
+// serialised load / math / barrier / math / store inside every CTA, measured slower, and is no longer shipped.)
 //
 // Rows reach the SM through a per-warp shared-memory slot filled by bulk async copies (cp.async.bulk +
 // mbarrier): while a warp works on one row pair from registers, the copy of its next pair is already in

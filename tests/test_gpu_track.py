@@ -140,3 +140,29 @@ def test_frames_produced_on_another_stream_are_ordered():
         frame.copy_(host[k], non_blocking=True)
         got, _ = trk.track([frame])
         np.testing.assert_array_equal(got, want[k])
+
+
+@pytest.mark.parametrize("switch", ["VIPT_NO_ZEROCOPY", "VIPT_NO_SPECULATION"])
+def test_host_path_switches(monkeypatch, switch):
+    """The two host-frame switches (read once when the engine is created): page-locked frames uploaded by per-sequence
+    2-D copies instead of the zero-copy gather kernel / no speculative copy-engine upload next to the running step.
+    Same boxes as the device-frame path, pipelined call pattern included."""
+    monkeypatch.setenv(switch, "1")
+    B, T = 2, 5
+    sd = synth.weight_set("peaked", "vipt_deep")
+    seqs = [synth.synthetic_sequence(60 + i, T, "rgbt") for i in range(B)]
+    pinned = [[torch.from_numpy(f).pin_memory() for f in s[0]] for s in seqs]
+    a = BatchedViPTTracker(sd, B, "vipt_deep", use_graph=False)
+    monkeypatch.delenv(switch)
+    b = BatchedViPTTracker(sd, B, "vipt_deep", use_graph=False)
+    a.initialize([p[0] for p in pinned], [s[1] for s in seqs])
+    b.initialize([torch.from_numpy(s[0][0]).cuda() for s in seqs], [s[1] for s in seqs])
+    want = [b.track([torch.from_numpy(s[0][t]).cuda() for s in seqs])[0].copy() for t in range(1, T)]
+    a.track_async([p[1] for p in pinned])
+    got = []
+    for t in range(2, T):                      # one step in flight: enqueue t, collect t - 1
+        a.track_async([p[t] for p in pinned])
+        got.append(a.collect()[0].copy())
+    got.append(a.collect()[0].copy())
+    for g, w in zip(got, want):
+        np.testing.assert_array_equal(g, w)
