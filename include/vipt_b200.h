@@ -93,6 +93,12 @@ int vipt_engine_init(void* engine, const void* const* frame_dev_ptrs_host, const
 int vipt_engine_track_enqueue(void* engine, const void* frame_ptrs_dev, int use_graph, void* stream);
 /* copies the latest boxes (B,4) [x,y,w,h] and best scores (B) to host memory and synchronises the stream. */
 int vipt_engine_results(void* engine, double* boxes_host, float* scores_host, void* stream);
+/* Per-sequence error flags (B ints: 0 or VIPT_ERR_SMALL_BOX), sticky until the next init.  A sequence whose box
+ * collapses ('Too small bounding box.', processing_utils.py:34) keeps its last crop and no longer disturbs the others:
+ * init / results / collect report VIPT_ERR_SMALL_BOX ONCE per newly failing sequence; this call tells which ones and
+ * lowers the engine-wide flag, so the caller can drop them and keep tracking the rest (the reference loses only the
+ * offending sequence's process, RGBT_workspace/test_rgbt_mgpus.py:66-117). */
+int vipt_engine_slot_errors(void* engine, int* slot_err_host, void* stream);
 /* HOST-frame variants (the reference hands ViPTTrack host ndarrays, vipt.py:41,64): frames are B host pointers to
  * uint8 (H,W,6) images.  init_host uploads the whole frames into engine-owned device buffers; track_host brings in
  * only the rectangle the search crop can read (processing_utils.py:32-47) and enqueues one step.  Page-locked

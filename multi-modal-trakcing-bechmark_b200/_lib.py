@@ -36,6 +36,7 @@ SIGNATURES = {
     "vipt_engine_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]),
     "vipt_engine_init": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "vipt_engine_track_enqueue": (c_int, [c_void_p, c_void_p, c_int, c_void_p]),
+    "vipt_engine_slot_errors": (c_int, [c_void_p, c_void_p, c_void_p]),
     "vipt_engine_init_host": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "vipt_engine_track_host": (c_int, [c_void_p, c_void_p, c_int, ctypes.POINTER(c_i64), c_void_p]),
     "vipt_engine_collect": (c_int, [c_void_p, c_void_p, c_void_p, ctypes.POINTER(c_i64)]),

@@ -139,6 +139,17 @@ int vipt_engine_results(void* ev, double* boxes_host, float* scores_host, void* 
   e->res_pending = 0;            // the latest state has been read: earlier uncollected steps are dropped
   return herr;
 }
+int vipt_engine_slot_errors(void* ev, int* slot_err_host, void* stream) {
+  vipt::Engine* e = (vipt::Engine*)ev;
+  if (!e || !slot_err_host || !e->finalized) return VIPT_ERR_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (cudaMemcpyAsync(slot_err_host, e->err + 1, sizeof(int) * e->B, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+      cudaMemsetAsync(e->err, 0, sizeof(int), st) != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess) {
+    set_err(cudaGetErrorString(cudaGetLastError()));
+    return VIPT_ERR_LAUNCH;
+  }
+  return VIPT_OK;
+}
 int vipt_engine_init_host(void* e, const void* const* host_frames, const int* hw_host, const double* boxes_host,
                           void* stream) {
   if (!e || !host_frames || !hw_host || !boxes_host) return VIPT_ERR_ARG;

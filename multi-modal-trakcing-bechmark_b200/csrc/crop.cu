@@ -69,7 +69,8 @@ constexpr int kCropPix = 8;
 __global__ void __launch_bounds__(256)
 crop_kernel(const uint8_t* const* __restrict__ frames, const int* __restrict__ frame_hw,
             const double* __restrict__ boxes, double factor, int S, int row_base, int rows_per_seq,
-            op_t* __restrict__ apatch, int64_t group_stride, double* __restrict__ geom, int* __restrict__ err) {
+            op_t* __restrict__ apatch, int64_t group_stride, double* __restrict__ geom, int* __restrict__ err,
+            int* __restrict__ slot_err) {
   pdl_trigger();       // programmatic dependent launch protocol (sm100_ptx.cuh); first kernel of a step: its
   pdl_wait();          // predecessor is the head of the previous step, which wrote the box state read here
   const int b = blockIdx.y;
@@ -94,7 +95,12 @@ crop_kernel(const uint8_t* const* __restrict__ frames, const int* __restrict__ f
   __syncthreads();
   const double csd = s_geo[0];
   if (!(csd >= 1.0)) {           // 'Too small bounding box.' (processing_utils.py:34)
-    if (unit == 0) atomicExch(err, VIPT_ERR_SMALL_BOX);
+    // the engine-wide flag is raised once per failing sequence (its per-slot flag is sticky until the next initialize),
+    // so the sequences that keep tracking are not reported again on every later step
+    if (unit == 0 && threadIdx.x == 0) {
+      if (!slot_err) atomicExch(err, VIPT_ERR_SMALL_BOX);
+      else if (slot_err[b] == 0) { slot_err[b] = VIPT_ERR_SMALL_BOX; atomicExch(err, VIPT_ERR_SMALL_BOX); }
+    }
     return;
   }
   const int cs = s_gi[0];
@@ -196,12 +202,12 @@ patchify_kernel(const float* __restrict__ img, int S, int row_base, int rows_per
 
 int launch_crop(const uint8_t* const* frames, const int* frame_hw, const double* boxes, double factor, int S,
                 int row_base, int rows_per_seq, void* apatch, int64_t group_stride, double* geom, int* err, int B,
-                cudaStream_t st) {
+                cudaStream_t st, int* slot_err) {
   if ((S != 128 && S != 256) || crop_prepare()) return VIPT_ERR_ARG;
   if ((group_stride & 7) || (reinterpret_cast<uintptr_t>(apatch) & 15)) return VIPT_ERR_ARG;      // 16-byte stores
   dim3 grid(S * S / (kCropPix * 256), B);
   const cudaError_t e_ = launch_pdl(crop_kernel, grid, 256, 0, st, frames, frame_hw, boxes, factor, S, row_base, rows_per_seq,
-                                    reinterpret_cast<op_t*>(apatch), group_stride, geom, err);
+                                    reinterpret_cast<op_t*>(apatch), group_stride, geom, err, slot_err);
   return e_ == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
 }
 

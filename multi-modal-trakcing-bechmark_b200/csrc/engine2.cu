@@ -64,7 +64,7 @@ int Engine::finalize_buffers() {
   AL(feat16, __half, RH * 768); AL(feat32, float, R * 768);
   AL(h1, __half, RH * 768); AL(h2, __half, RH * 384); AL(h3, __half, RH * 192); AL(h4, __half, RH * 96);
   AL(giA, int, RH); AL(giB, int, RH); AL(perm, int, RH); AL(removed, int, 3 * RH); AL(slot_of_pos, int, RH);
-  AL(ident, int, RH); AL(err, int, 1);
+  AL(ident, int, RH); AL(err, int, 1 + B);      // [0] engine-wide flag, [1 + b] sticky per-sequence flags
   AL(score_map, float, RH); AL(size_map, float, 2 * RH); AL(offset_map, float, 2 * RH);
   AL(pred_boxes, float, B * 4); AL(out_scores, float, B);
   AL(state, double, B * 4); AL(geom_z, double, B * 4); AL(geom_x, double, B * 4); AL(out_boxes, double, B * 4);
@@ -76,7 +76,7 @@ int Engine::finalize_buffers() {
     std::vector<int> id(RH);
     for (size_t i = 0; i < RH; ++i) id[i] = (int)(i % kLensX);
     CK(cudaMemcpy(ident, id.data(), RH * 4, cudaMemcpyHostToDevice));
-    CK(cudaMemset(err, 0, 4));
+    CK(cudaMemset(err, 0, 4 * (1 + B)));
     RET(crop_prepare());
     CK(cudaMemset(removed, 0, 3 * RH * 4));
   }
@@ -258,10 +258,10 @@ int Engine::init_sequences(const void* const* frames_host_ptrs, const int* hw_ho
   CK(cudaMemcpyAsync(state, boxes_host, sizeof(double) * 4 * B, cudaMemcpyHostToDevice, st));
   host_state.assign(boxes_host, boxes_host + 4 * B);
   mirror_valid = true;
-  CK(cudaMemsetAsync(err, 0, 4, st));
+  CK(cudaMemsetAsync(err, 0, 4 * (1 + B), st));
   const int64_t gs = (int64_t)B * kLensFull * 768;
   // template: factor 2.0 -> 128 x 128 (vipt.py:43-48); the crop is kept as the resident patch rows 0..63
-  RET(launch_crop(frame_ptrs, frame_hw, state, 2.0, 128, 0, kLensFull, apatch, gs, geom_z, err, B, st));
+  RET(launch_crop(frame_ptrs, frame_hw, state, 2.0, 128, 0, kLensFull, apatch, gs, geom_z, err, B, st, err + 1));
   int herr = 0;
   CK(cudaMemcpyAsync(&herr, err, 4, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
@@ -280,7 +280,7 @@ int Engine::track_enqueue(const void* frame_ptrs_dev, bool use_graph, cudaStream
     // search: factor 4.0 -> 256 x 256 around the current state (vipt.py:67-69)
     pdl_select(B, num_sms);
     prof_begin(K_CROP, s);
-    RET(launch_crop(frame_ptrs, frame_hw, state, 4.0, 256, kLensT, kLensFull, apatch, gs, geom_x, err, B, s));
+    RET(launch_crop(frame_ptrs, frame_hw, state, 4.0, 256, kLensT, kLensFull, apatch, gs, geom_x, err, B, s, err + 1));
     prof_end(s);
     return run_backbone_head(true, false, 0, s);
   };

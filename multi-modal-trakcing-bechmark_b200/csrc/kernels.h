@@ -10,7 +10,7 @@ namespace vipt {
 
 int launch_crop(const uint8_t* const* frames, const int* frame_hw, const double* boxes, double factor, int S,
                 int row_base, int rows_per_seq, void* apatch, int64_t group_stride, double* geom, int* err, int B,
-                cudaStream_t st);
+                cudaStream_t st, int* slot_err = nullptr);      // slot_err (B) optional: sticky per-sequence flags
 int crop_prepare();      // uploads the normalisation table; called outside stream capture (Engine::finalize, first launch_crop)
 int launch_patchify(const float* img, int S, int row_base, int rows_per_seq, void* apatch, int64_t group_stride, int B,
                     cudaStream_t st);

@@ -98,28 +98,66 @@ def run_sequences(seq_names, seq_home, dataset_name, state_dict, save_dir, kind=
             gen_config_rgbe(seq_home + '/' + name, dataset_name)[:3]
         cfgs[name] = (cfg, path)
         todo.append(name)
-    mine = [todo[i] for i in shard.assign_sequences([len(cfgs[n][0][0]) for n in todo], world)[rank]] if todo else []
+    # like `zip(RGB_img_list, T_img_list)` (test_rgbt_mgpus.py:98): a sequence is as long as its shorter image list
+    nfr = {n: min(len(cfgs[n][0][0]), len(cfgs[n][0][1])) for n in todo}
+    mine = [todo[i] for i in shard.assign_sequences([nfr[n] for n in todo], world)[rank]] if todo else []
     results = {}
+    failed = {}
     trackers = {}
-    for group in plan_groups([len(cfgs[n][0][0]) for n in mine], batch):
-        names = [mine[i] for i in group]
-        nb = len(names)
+
+    def tracker_for(nb):
         if nb not in trackers:                       # the engine is built for a fixed number of slots
             trackers[nb] = BatchedViPTTracker(state_dict, nb, prompt_type, use_graph=True)
-        trk = trackers[nb]
-        lists = [cfgs[n][0] for n in names]
-        res = [new_result(len(l[0]), l[2]) for l in lists]
-        T = max(len(l[0]) for l in lists)
-        frames = [load_frame(l[0][0], l[1][0], xtype) for l in lists]
-        trk.initialize(frames, [l[2][0].tolist() for l in lists])
+        return trackers[nb]
+
+    def small_box(e):
+        return "Too small bounding box" in str(e)
+
+    for group in plan_groups([nfr[n] for n in mine], batch):
+        names = [mine[i] for i in group]
+        # initialize; a sequence whose first box is degenerate ('Too small bounding box.', processing_utils.py:34) is
+        # dropped -- in the reference only that sequence's process dies -- and the rest of the group starts again
+        while names:
+            trk = tracker_for(len(names))
+            lists = [cfgs[n][0] for n in names]
+            frames = [load_frame(l[0][0], l[1][0], xtype) for l in lists]
+            try:
+                trk.initialize(frames, [l[2][0].tolist() for l in lists])
+                break
+            except Exception as e:
+                if not small_box(e):
+                    raise
+                bad = trk.failed_slots()
+                for k in bad:
+                    failed[names[k]] = "Too small bounding box. (frame 0)"
+                    print("vipt_b200.driver: %s: Too small bounding box. (frame 0) -- sequence skipped" % names[k])
+                names = [n for k, n in enumerate(names) if k not in bad]
+        if not names:
+            continue
+        res = [new_result(nfr[n], cfgs[n][0][2]) for n in names]
+        alive = [True] * len(names)
+        T = max(nfr[n] for n in names)
         for t in range(1, T):
-            # a finished sequence keeps its last frame; its boxes are no longer recorded
-            frames = [load_frame(l[0][t], l[1][t], xtype) if t < len(l[0]) else frames[k] for k, l in enumerate(lists)]
-            boxes, _ = trk.track(frames)
-            for k, l in enumerate(lists):
-                if t < len(l[0]):
+            # a finished (or failed) sequence keeps its last frame; its boxes are no longer recorded
+            frames = [load_frame(l[0][t], l[1][t], xtype) if (t < nfr[n] and alive[k]) else frames[k]
+                      for k, (n, l) in enumerate(zip(names, lists))]
+            try:
+                boxes, _ = trk.track(frames)
+            except Exception as e:
+                if not small_box(e):
+                    raise
+                for k in trk.failed_slots():          # only the offending sequences are lost (their slots idle on)
+                    if alive[k]:
+                        alive[k] = False
+                        failed[names[k]] = "Too small bounding box. (frame %d)" % t
+                        print("vipt_b200.driver: %s: Too small bounding box. (frame %d) -- sequence dropped" % (names[k], t))
+                boxes, _ = trk.collect()
+            for k, n in enumerate(names):
+                if t < nfr[n] and alive[k]:
                     res[k][t] = boxes[k]
-        for n, r in zip(names, res):
-            save_result(cfgs[n][1], r, kind)
-            results[n] = r
+        for k, (n, r) in enumerate(zip(names, res)):
+            if alive[k]:
+                save_result(cfgs[n][1], r, kind)
+                results[n] = r
+    run_sequences.failed = failed
     return results

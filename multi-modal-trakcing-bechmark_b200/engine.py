@@ -140,6 +140,13 @@ class NativeEngine:
             self._host_keepalive.popleft()
         return boxes, scores, n.value
 
+    def slot_errors(self):
+        """(B,) int32: sticky per-sequence error flags (0 or -5 'Too small bounding box.'); lowers the engine-wide flag."""
+        out = np.zeros(self.batch, np.int32)
+        _lib.check(self.L.vipt_engine_slot_errors(self.h, out.ctypes.data_as(ctypes.c_void_p), self._sp()),
+                   "vipt_engine_slot_errors")
+        return out
+
     def set_state(self, boxes):
         bx = np.ascontiguousarray(np.asarray(boxes, np.float64).reshape(self.batch, 4))
         _lib.check(self.L.vipt_engine_set_state(self.h, bx.ctypes.data_as(ctypes.c_void_p), self._sp()),

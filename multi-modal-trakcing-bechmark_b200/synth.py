@@ -47,8 +47,23 @@ WEIGHT_SETS = {"flat": 0.02, "peaked": 0.06}
 
 
 def weight_set(name: str, prompt_type: str = "vipt_deep", seed: int = 0):
-    """state_dict of a named weight set (WEIGHT_SETS)."""
+    """state_dict of a named weight set (WEIGHT_SETS); "outlier" = the peaked set with outlier channels (below)."""
+    if name == "outlier":
+        return with_outlier_channels(synthetic_state_dict(prompt_type, seed, qkv_std=WEIGHT_SETS["peaked"]))
     return synthetic_state_dict(prompt_type, seed, qkv_std=WEIGHT_SETS[name])
+
+
+def with_outlier_channels(sd, scale=40.0, channels=(5, 301, 640), blocks=(1, 4, 7, 10)):
+    """Trained ViTs carry a few channels whose LayerNorm gain is tens of times the typical one (and matching large
+    fc1 weights), which is what stresses 16-bit GEMM operands: the LayerNorm outputs of those channels reach
+    ~scale * 3, the fc1 pre-activations and the GELU outputs (fp16 in the engine) grow accordingly.  In place."""
+    for i in blocks:
+        p = "backbone.blocks.%d." % i
+        for c in channels:
+            sd[p + "norm1.weight"][c] *= scale
+            sd[p + "norm2.weight"][c] *= scale
+            sd[p + "mlp.fc1.weight"][:, c] *= 4.0
+    return sd
 
 
 def synthetic_state_dict(prompt_type: str = "vipt_deep", seed: int = 0, qkv_std: float = 0.02):

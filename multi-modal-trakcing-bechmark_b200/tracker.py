@@ -78,6 +78,11 @@ class BatchedViPTTracker:
         for f in frames:
             f.record_stream(es)
 
+    def failed_slots(self):
+        """Indices of the sequences that raised 'Too small bounding box.' since the last initialize (their results are
+        meaningless from that frame on; the other sequences are unaffected).  Lowers the engine's error flag."""
+        return [int(i) for i in np.nonzero(self.engine.slot_errors())[0]]
+
     def set_state(self, boxes):
         """Override the box state of every sequence (teacher-forced evaluation)."""
         self.engine.set_state(boxes)
@@ -108,8 +113,8 @@ class BatchedViPTTracker:
         With page-locked host frames up to 4 steps may be in flight: enqueue step t+1, then collect step t, so the
         host never stalls the device (the rectangle of step t+1 is evaluated on the device from step t's boxes)."""
         if self._pending_host > 0:
+            self._pending_host -= 1          # the step leaves the ring even when it reports 'Too small bounding box.'
             boxes, scores, n = self.engine.collect()
-            self._pending_host -= 1
             self.h2d_bytes = n
         else:
             boxes, scores = self.engine.results()

@@ -31,7 +31,7 @@ from . import vipt_oracle as vo
 # `ce_boundary_score_rel_err`): p99 3.0e-4..5.4e-4, max 6.4e-4 (flat); p99 4.2e-3..8.2e-3, max 1.3e-2 (peaked).
 # TAU_CE ~ 1.5 x the largest error seen; tests/test_gpu_parity.py asserts max error < TAU_CE <= 6 x the measured p99,
 # so the exemption cannot be wider than the demonstrated arithmetic error.
-TAU_CE_BY_SET = {"flat": 1e-3, "peaked": 2e-2}
+TAU_CE_BY_SET = {"flat": 1e-3, "peaked": 2e-2, "outlier": 2e-2}
 TAU_AM = 2e-3     # relative gap of the reference's top-2 windowed responses
 TOL_MAP = 1e-2
 TOL_BOX = 0.5

@@ -117,3 +117,25 @@ def test_api_errors():
         m.load_state_dict({"backbone.norm.weight": torch.zeros(768)}, strict=True)
     with pytest.raises(ValueError):
         build_viptrack({"MODEL": {"HEAD": {"TYPE": "MLPX"}}})
+
+
+def test_outlier_channels_fp16_range():
+    """16-bit operand range: weights with outlier LayerNorm gains (x40 on a few channels of four
+    blocks, fc1 columns x4 -- the pattern trained ViTs show) drive the fp16 GEMM operands two orders of magnitude above
+    the random-init range.  The saturating converts (cvt.rn.satfinite.f16x2.f32) must stay far from their clamp in
+    every fp16 buffer, and the forward must still meet the parity bar on every sample."""
+    B = 4
+    gen = torch.Generator().manual_seed(11)
+    z = torch.randn(B, 6, 128, 128, generator=gen); x = torch.randn(B, 6, 256, 256, generator=gen)
+    m = _model("vipt_deep", "outlier")
+    out = m.forward(z.cuda(), x.cuda(), vo.ce_template_mask(B).cuda())
+    eng = m.engine(B)
+    peak = {}
+    for name in ("xn", "qkv", "att", "hbuf", "dbuf", "feat16", "h1"):
+        t = eng.buffer(name).float()
+        assert torch.isfinite(t).all(), name
+        peak[name] = t.abs().max().item()
+    print("fp16 buffer maxima:", {k: round(v, 1) for k, v in peak.items()})
+    assert peak["xn"] > 50.0                      # the outliers are really there ...
+    assert max(peak.values()) < 0.25 * 65504      # ... and two binades below the fp16 clamp
+    _check_model(m, out, z, x, "vipt_deep", "outlier")
