@@ -53,7 +53,7 @@ def weight_set(name: str, prompt_type: str = "vipt_deep", seed: int = 0):
     return synthetic_state_dict(prompt_type, seed, qkv_std=WEIGHT_SETS[name])
 
 
-def with_outlier_channels(sd, scale=40.0, channels=(5, 301, 640), blocks=(1, 4, 7, 10)):
+def with_outlier_channels(sd, scale=40.0, channels=(5, 301, 640), blocks=(1, 4, 7, 11)):
     """Trained ViTs carry a few channels whose LayerNorm gain is tens of times the typical one (and matching large
     fc1 weights), which is what stresses 16-bit GEMM operands: the LayerNorm outputs of those channels reach
     ~scale * 3, the fc1 pre-activations and the GELU outputs (fp16 in the engine) grow accordingly.  In place."""
