@@ -33,10 +33,23 @@
 // (the register-only version spent 42 % of its time waiting for the loads of the pair it was about to use).
 #include <cooperative_groups.h>
 
+#include <algorithm>
+#include <vector>
+
 #include "kernels.h"
 #include "sm100_ptx.cuh"
 
 namespace cg = cooperative_groups;
+
+#ifdef PC_TRACE      // timing experiments only: per-CTA phase timestamps (printed by launch_prompt_coop)
+__device__ long long g_pc_trace[160 * 8];
+#define PCT(ev)                                                                        \
+  do {                                                                                 \
+    if (threadIdx.x == 0) g_pc_trace[blockIdx.x * 8 + (ev)] = clock64();               \
+  } while (0)
+#else
+#define PCT(ev)
+#endif
 
 namespace vipt {
 
@@ -116,6 +129,7 @@ prompt_coop_kernel(float* __restrict__ x, const op_t* __restrict__ delta, int B,
   uint64_t* wbar = s_bar + kWarps;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  PCT(0);
   const int lens_x = lens_full - lens_t;
   const int total = B * n_cur;
   int rpc = (total + (int)gridDim.x - 1) / (int)gridDim.x;
@@ -151,6 +165,7 @@ prompt_coop_kernel(float* __restrict__ x, const op_t* __restrict__ delta, int B,
   pdl_trigger();                 // the next kernel's CTAs may start their prologue (sm100_ptx.cuh); this kernel itself is a
                                  // cooperative launch without the programmatic attribute, so it has nothing to wait for
   mbar_wait(wbar, 0);
+  PCT(1);
   const float smooth = s_fold[kSmooth];
 
   // ------------------------------------------------------------------ phase 1: x0 per row
@@ -238,8 +253,11 @@ prompt_coop_kernel(float* __restrict__ x, const op_t* __restrict__ delta, int B,
       if ((lane & 3) == 0 && (i == 0 || two)) X0[(size_t)(r0 + i) * 8 + (lane >> 2)] = c * rstd + s_fold[kCA + (lane >> 2)];
     }
   }
+  __syncthreads();
+  PCT(2);
   __threadfence();
   cg::this_grid().sync();
+  PCT(3);
 
   // ------------------------------------------------------------------ phase 2, sequence by sequence
   if (row_lo >= row_hi) return;
@@ -251,42 +269,62 @@ prompt_coop_kernel(float* __restrict__ x, const op_t* __restrict__ delta, int B,
     // Fovea softmax statistics of sequence b (all its kept rows, wherever they were computed):
     // thread = (channel k, part); two block reductions (max, then sum of exp)
     {
+      // thread = (channel k, part); lanes of a warp hold 4 parts x 8 channels: two shuffle steps fold the parts of a
+      // warp, the 16 warp results go through shared memory, 16 threads finish (16 terms each, fixed order)
       const int k = tid & 7, part = tid >> 3;
       const float* x0b = X0 + (size_t)b * n_cur * 8;
+      float l[5];                                // this thread's logits (n_cur <= 320: at most 5 rows per thread)
       float m[2] = {-INFINITY, -INFINITY};
-      for (int r = part; r < n_cur; r += kThreads / 8) {
-        const float l = __ldcg(x0b + r * 8 + k) * smooth;
-        m[r < lens_t ? 0 : 1] = fmaxf(m[r < lens_t ? 0 : 1], l);
+#pragma unroll
+      for (int i = 0; i < 5; ++i) {
+        const int r = part + i * (kThreads / 8);
+        l[i] = r < n_cur ? __ldcg(x0b + r * 8 + k) * smooth : -INFINITY;
+        if (r < lens_t) m[0] = fmaxf(m[0], l[i]); else m[1] = fmaxf(m[1], l[i]);
+      }
+#pragma unroll
+      for (int o = 8; o <= 16; o <<= 1) {
+        m[0] = fmaxf(m[0], __shfl_xor_sync(0xffffffffu, m[0], o));
+        m[1] = fmaxf(m[1], __shfl_xor_sync(0xffffffffu, m[1], o));
       }
       __syncthreads();                           // s_red / s_ms of the previous sequence are no longer read
-      s_red[tid * 2] = m[0]; s_red[tid * 2 + 1] = m[1];
+      if (lane < 8) { s_red[(warp * 8 + lane) * 2] = m[0]; s_red[(warp * 8 + lane) * 2 + 1] = m[1]; }
       __syncthreads();
       if (tid < 16) {
         const int dom = tid >> 3, kk = tid & 7;
         float M = -INFINITY;
-        for (int p = 0; p < kThreads / 8; ++p) M = fmaxf(M, s_red[(p * 8 + kk) * 2 + dom]);
+        for (int w = 0; w < kWarps; ++w) M = fmaxf(M, s_red[(w * 8 + kk) * 2 + dom]);
         const int n_removed = dom == 1 ? lens_x - (n_cur - lens_t) : 0;
         if (n_removed > 0) M = fmaxf(M, smooth * s_fold[kCA + kk]);
         s_ms[(dom * 8 + kk) * 2] = M;
       }
       __syncthreads();
       float sm[2] = {0.f, 0.f};
-      for (int r = part; r < n_cur; r += kThreads / 8) {
-        const int dom = r < lens_t ? 0 : 1;
-        sm[dom] += expf(__ldcg(x0b + r * 8 + k) * smooth - s_ms[(dom * 8 + k) * 2]);
+#pragma unroll
+      for (int i = 0; i < 5; ++i) {
+        const int r = part + i * (kThreads / 8);
+        if (r < n_cur) {                         // (no dynamically indexed register arrays: they live in local memory)
+          if (r < lens_t) sm[0] += expf(l[i] - s_ms[k * 2]);
+          else sm[1] += expf(l[i] - s_ms[(8 + k) * 2]);
+        }
       }
-      s_red[2 * kThreads + tid * 2] = sm[0]; s_red[2 * kThreads + tid * 2 + 1] = sm[1];
+#pragma unroll
+      for (int o = 8; o <= 16; o <<= 1) {
+        sm[0] += __shfl_xor_sync(0xffffffffu, sm[0], o);
+        sm[1] += __shfl_xor_sync(0xffffffffu, sm[1], o);
+      }
+      if (lane < 8) { s_red[2 * kThreads + (warp * 8 + lane) * 2] = sm[0]; s_red[2 * kThreads + (warp * 8 + lane) * 2 + 1] = sm[1]; }
       __syncthreads();
       if (tid < 16) {
         const int dom = tid >> 3, kk = tid & 7;
         float S = 0.f;
-        for (int p = 0; p < kThreads / 8; ++p) S += s_red[2 * kThreads + (p * 8 + kk) * 2 + dom];
+        for (int w = 0; w < kWarps; ++w) S += s_red[2 * kThreads + (w * 8 + kk) * 2 + dom];
         const int n_removed = dom == 1 ? lens_x - (n_cur - lens_t) : 0;
         if (n_removed > 0) S += (float)n_removed * expf(smooth * s_fold[kCA + kk] - s_ms[(dom * 8 + kk) * 2]);
         s_ms[(dom * 8 + kk) * 2 + 1] = 1.0f / S;
       }
       __syncthreads();
     }
+    PCT(4);
     for (int r0 = lo + 2 * warp; r0 < hi; r0 += 2 * kWarps) {
       const bool two = r0 + 1 < hi;
       float4 v[2][6];
@@ -331,12 +369,12 @@ prompt_coop_kernel(float* __restrict__ x, const op_t* __restrict__ delta, int B,
           F[((size_t)b * lens_full + pos) * 8 + k] = fk;       // all 8 lanes of a row have read F[pos] before this
         }
       }
-      float f[2][8], s[2] = {0.f, 0.f};
+      float f[2][8];
 #pragma unroll
       for (int i = 0; i < 2; ++i)
 #pragma unroll
         for (int k = 0; k < 8; ++k) f[i][k] = __shfl_sync(0xffffffffu, fk, i * 8 + k);
-      uint64_t f2[2][8], s2[2] = {0ull, 0ull};    // packed fp32x2 FMAs for the 8 -> 768 projection (see phase 1)
+      uint64_t f2[2][8], s2[2] = {0ull, 0ull}, q2[2] = {0ull, 0ull};    // packed fp32x2 FMAs (see phase 1)
 #pragma unroll
       for (int i = 0; i < 2; ++i)
 #pragma unroll
@@ -363,11 +401,10 @@ prompt_coop_kernel(float* __restrict__ x, const op_t* __restrict__ delta, int B,
           upk2(v01, v[i][j].x, v[i][j].y);
           upk2(v23, v[i][j].z, v[i][j].w);
           s2[i] = add2(s2[i], add2(v01, v23));
+          q2[i] = fma2(v01, v01, q2[i]);          // sum of squares in the same pass: one reduction round instead of two
+          q2[i] = fma2(v23, v23, q2[i]);
         }
       }
-#pragma unroll
-      for (int i = 0; i < 2; ++i) s[i] += hsum2(s2[i]);
-      float mean[2], rstd[2], qv[2] = {0.f, 0.f};
 #pragma unroll
       for (int i = 0; i < 2; ++i) {
         if (i == 1 && !two) break;
@@ -376,19 +413,25 @@ prompt_coop_kernel(float* __restrict__ x, const op_t* __restrict__ delta, int B,
 #pragma unroll
         for (int j = 0; j < 6; ++j) xo[lane + 32 * j] = v[i][j];
       }
-      pc_warp_sum2(s[0], s[1]);                  // both rows' butterflies in flight together (row 1 is zeros if !two)
-      mean[0] = s[0] * (1.0f / D);
-      mean[1] = s[1] * (1.0f / D);
+      // LayerNorm statistics of both rows from (sum, sum of squares): four butterflies in flight together.  var =
+      // E[v^2] - mean^2 in fp32 (|mean| << rms in the residual stream: relative error ~1e-6, far below the fp16 output)
+      float st4[4] = {hsum2(s2[0]), hsum2(s2[1]), hsum2(q2[0]), hsum2(q2[1])};
 #pragma unroll
-      for (int i = 0; i < 2; ++i)
+      for (int o = 16; o > 0; o >>= 1) {
+        float t[4];
 #pragma unroll
-        for (int j = 0; j < 6; ++j) {
-          const float a0 = v[i][j].x - mean[i], a1 = v[i][j].y - mean[i], a2 = v[i][j].z - mean[i], a3 = v[i][j].w - mean[i];
-          qv[i] += a0 * a0 + a1 * a1 + a2 * a2 + a3 * a3;
-        }
-      pc_warp_sum2(qv[0], qv[1]);
-      rstd[0] = rsqrtf(qv[0] * (1.0f / D) + kLnEps);
-      rstd[1] = rsqrtf(qv[1] * (1.0f / D) + kLnEps);
+        for (int c = 0; c < 4; ++c) t[c] = __shfl_xor_sync(0xffffffffu, st4[c], o);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) st4[c] += t[c];
+      }
+      float sc[2], sh[2];                        // xn = (v * sc + sh) * g + be
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        const float mean = st4[i] * (1.0f / D);
+        const float var = fmaxf(st4[2 + i] * (1.0f / D) - mean * mean, 0.f);
+        sc[i] = rsqrtf(var + kLnEps);
+        sh[i] = -mean * sc[i];
+      }
 #pragma unroll
       for (int j = 0; j < 6; ++j) {              // norm1 scale / shift read once for both rows
         const float4 g = s_g1[lane + 32 * j];
@@ -397,13 +440,15 @@ prompt_coop_kernel(float* __restrict__ x, const op_t* __restrict__ delta, int B,
         for (int i = 0; i < 2; ++i) {
           if (i == 1 && !two) break;
           uint2 u;
-          u.x = pack_op2((v[i][j].x - mean[i]) * rstd[i] * g.x + be.x, (v[i][j].y - mean[i]) * rstd[i] * g.y + be.y);
-          u.y = pack_op2((v[i][j].z - mean[i]) * rstd[i] * g.z + be.z, (v[i][j].w - mean[i]) * rstd[i] * g.w + be.w);
+          u.x = pack_op2(fmaf(fmaf(v[i][j].x, sc[i], sh[i]), g.x, be.x), fmaf(fmaf(v[i][j].y, sc[i], sh[i]), g.y, be.y));
+          u.y = pack_op2(fmaf(fmaf(v[i][j].z, sc[i], sh[i]), g.z, be.z), fmaf(fmaf(v[i][j].w, sc[i], sh[i]), g.w, be.w));
           reinterpret_cast<uint2*>(xn + ((size_t)r0 + i) * D)[lane + 32 * j] = u;
         }
       }
     }
   }
+  __syncthreads();
+  PCT(5);
 }
 
 int launch_prompt_coop(float* x, const void* delta, int n_cur, const int* gi, float* F, float* X0, const float* wg_a,
@@ -416,7 +461,7 @@ int launch_prompt_coop(float* x, const void* delta, int n_cur, const int* gi, fl
             cudaSuccess || ctas_per_sm < 1)
       return VIPT_ERR_LAUNCH;
   }
-  if (!delta || n_cur < lens_t || n_cur > lens_full) return VIPT_ERR_ARG;
+  if (!delta || n_cur < lens_t || n_cur > lens_full || lens_full > 5 * (pc::kThreads / 8)) return VIPT_ERR_ARG;
   const int total = B * n_cur;
   int grid = ctas_per_sm * num_sms;
   const int want = (total + 2 * pc::kWarps - 1) / (2 * pc::kWarps);     // at least one row pair per warp
@@ -427,6 +472,24 @@ int launch_prompt_coop(float* x, const void* delta, int n_cur, const int* gi, fl
   if (cudaLaunchCooperativeKernel((const void*)prompt_coop_kernel, dim3(grid), dim3(pc::kThreads), args, pc::kSmemBytes, st) !=
       cudaSuccess)
     return VIPT_ERR_LAUNCH;
+#ifdef PC_TRACE
+  static int launches = 0;
+  if (++launches == 25 || launches == 30) {
+    cudaDeviceSynchronize();
+    static long long h[160 * 8];
+    cudaMemcpyFromSymbol(h, g_pc_trace, sizeof(h));
+    // clock64 is per SM: only differences inside a CTA mean something
+    auto stat = [&](int e1, int e0, const char* what) {
+      std::vector<long long> d;
+      for (int c = 0; c < grid; ++c) d.push_back(h[c * 8 + e1] - h[c * 8 + e0]);
+      std::sort(d.begin(), d.end());
+      fprintf(stderr, "  %-28s min %7lld  p50 %7lld  p90 %7lld  max %7lld clk\n", what, d[0], d[d.size() / 2], d[d.size() * 9 / 10], d.back());
+    };
+    fprintf(stderr, "prompt_coop n_cur %d grid %d\n", n_cur, grid);
+    stat(1, 0, "prologue (weights staged)"); stat(2, 1, "phase 1"); stat(3, 2, "grid barrier"); stat(5, 3, "phase 2 (stats + rows)");
+    stat(5, 0, "whole CTA");
+  }
+#endif
   return VIPT_OK;
 }
 
