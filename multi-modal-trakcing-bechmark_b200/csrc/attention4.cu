@@ -20,13 +20,17 @@
 //     their own producer warps, so a slot that is not free yet never delays a Q tile;
 //   * no integer divisions in the per-chunk loops.
 //
-//   warp 0        TMA producer, Q tiles (double-buffered)
-//   warp 3        TMA producer, K / V slots
-//   warp 1        score MMAs    S_k into TMEM buffer k % 3
-//   warp 2        value MMAs    O_k into TMEM buffer k % 2
-//   warps 4-11    softmax of even chunks (lane quarter = warp & 3, column half = (warp - 4) >> 2)
-//   warps 12-19   softmax of odd chunks
-//   warps 20-23   epilogue: online softmax in registers, output store, CE row (attn_blocks.py:44-53)
+//   warps 0-7     softmax of even chunks (lane quarter = warp & 3, column half = (warp >> 2) & 1)
+//   warps 8-15    softmax of odd chunks
+//   warps 16-19   epilogue: online softmax in registers, output store, CE row (attn_blocks.py:44-53)
+//   warp 20       TMA producer, Q tiles (double-buffered)
+//   warp 23       TMA producer, K / V slots
+//   warp 21       score MMAs    S_k into TMEM buffer k % 3
+//   warp 22       value MMAs    O_k into TMEM buffer k % 2
+// The producer / issuer warps have the HIGHEST warp ids on purpose: the warp arbiter of an SM sub-partition prefers
+// higher ids, and these warps need a few dozen issue slots per chunk at exactly the moment their barrier opens --
+// with the lowest ids they were served last behind four busy softmax warps (profiles/r2_attention4_trace.txt: P V MMAs
+// issued 1 000 - 3 000 clk after their operands were ready).
 #include "kernels.h"
 #include "sm100_ptx.cuh"
 
@@ -186,15 +190,15 @@ attention4_kernel(const __grid_constant__ CUtensorMap tm, op_t* __restrict__ out
     }
     fence_mbar_init();
   }
-  if (warp == 1) tmem_alloc<512>(tmem_slot);
+  if (warp == 21) tmem_alloc<512>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   pdl_trigger();
   pdl_wait();
-  if (warp < 4) {
+  if (warp >= 20) {
     reg_dec<kRegsWg0>();
-    if (warp == 0) {
+    if (warp == 20) {
       WORK();
       if (lane == 0 && total > 0) {
         // ------------------------------------------------------------ TMA producer: Q tiles
@@ -213,7 +217,7 @@ attention4_kernel(const __grid_constant__ CUtensorMap tm, op_t* __restrict__ out
           }
         }
       }
-    } else if (warp == 3) {
+    } else if (warp == 23) {
       WORK();
       if (lane == 0 && total > 0) {
         // ------------------------------------------------------------ TMA producer: K / V slots, load i -> slot i % 3
@@ -228,7 +232,7 @@ attention4_kernel(const __grid_constant__ CUtensorMap tm, op_t* __restrict__ out
             tma_load_3d(sKV + slot * kbytes + x * kBoxBytes, &tm, &bars[KV_FULL + slot], col, x * 64, b);
         }
       }
-    } else if (warp == 1) {
+    } else if (warp == 21) {
       // -------------------------------------------------------------- score MMAs: S_k = Q K_k^T, up to 3 chunks ahead.
       // The whole warp runs the loop (warp-uniform control flow, descriptor math in uniform registers); one elected
       // lane issues the MMAs and commits.
@@ -309,14 +313,14 @@ attention4_kernel(const __grid_constant__ CUtensorMap tm, op_t* __restrict__ out
         pp.advance(NC, T);
       }
     }
-  } else if (warp < 20) {
+  } else if (warp < 16) {
     // ---------------------------------------------------------------- softmax groups (even / odd chunks), 8 warps each:
     // lane quarter = warp & 3; the two warps of a quarter split the chunk's 32-column blocks (half 0 the first
     // ceil(nb / 2), half 1 the rest) and exchange their maxima through s_hmax (double-buffered by iteration parity:
     // a warp can be at most one group barrier ahead of its partner)
     WORK();
-    const int grp = (warp - 4) >> 3;
-    const int half = ((warp - 4) >> 2) & 1;
+    const int grp = warp >> 3;
+    const int half = (warp >> 2) & 1;
     const int wr = warp & 3;
     const int row = wr * 32 + lane;
     const uint32_t t_lane = tmem + ((uint32_t)(wr * 32) << 16);
@@ -434,7 +438,7 @@ attention4_kernel(const __grid_constant__ CUtensorMap tm, op_t* __restrict__ out
     WORK();
     const int wr = warp & 3;
     const int row = wr * 32 + lane;
-    const int et = threadIdx.x - 640;
+    const int et = threadIdx.x - 512;
     const uint32_t t_lane = tmem + ((uint32_t)(wr * 32) << 16);
     float acc[kHd];
     float m_run = 0.f, l_run = 0.f;
@@ -549,7 +553,7 @@ attention4_kernel(const __grid_constant__ CUtensorMap tm, op_t* __restrict__ out
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) {
+  if (warp == 21) {
     tc_fence_after();
     tmem_dealloc<512>(*tmem_slot);
   }
