@@ -166,8 +166,9 @@ int Engine::run_backbone_head(bool tracking, bool want_feat32, int debug_stop, c
     if (debug_stop > 0 && ++stage == debug_stop) return VIPT_OK; \
   } while (0)
   const size_t RH = (size_t)B * kLensX;
-  CK(cudaMemcpyAsync(giA, ident, RH * 4, cudaMemcpyDeviceToDevice, st));
-  CK(cudaMemcpyAsync(slot_of_pos, ident, RH * 4, cudaMemcpyDeviceToDevice, st));
+  // No per-step initialisation of the CE bookkeeping (two copy nodes per step until round 2): before the first
+  // candidate elimination the slot -> raster map IS the constant identity array, and slot_of_pos is written for all
+  // 256 positions by the first ce_topk launch before anything reads it.
   if (pe_pair) {
     LAUNCH(K_GEMM, gemm_launch(g_pe2[0], num_sms, st));
     LAUNCH(K_GEMM, gemm_launch(g_pe2[1], num_sms, st));
@@ -184,8 +185,8 @@ int Engine::run_backbone_head(bool tracking, bool want_feat32, int debug_stop, c
   STAGE_END();   // 2: x, xn, P after the input prompt
   float* x = xA;
   float* x_other = xB;
-  int* gi = giA;
-  int* gi_other = giB;
+  int* gi = ident;
+  int* gi_other = giA;
   int ce_idx = 0;
   for (int i = 0; i < kDepth; ++i) {
     const int n = n_tok[i];
@@ -211,7 +212,7 @@ int Engine::run_backbone_head(bool tracking, bool want_feat32, int debug_stop, c
                          slot_of_pos, ce_score + (size_t)ce_idx * RH, kLensX, B, st));
       LAUNCH(K_NORM, launch_ln_rows(x, n, dbuf, perm, kLensX, x_other, xn, L[i].ln2_g, L[i].ln2_b, B, nm, kLensT, st));
       float* t = x; x = x_other; x_other = t;
-      int* tg = gi; gi = gi_other; gi_other = tg;
+      int* tg = gi; gi = gi_other; gi_other = tg == ident ? giB : tg;      // the identity array is never a destination
       ++ce_idx;
     } else {
       LAUNCH(K_NORM, launch_ln_rows(x, n, dbuf, nullptr, 0, x, xn, L[i].ln2_g, L[i].ln2_b, B, nm, kLensT, st));
