@@ -70,6 +70,18 @@ int vipt_op_assemble_rgbx(const void* bgr_dev, const void* xbgr_dev, int H, int 
 int vipt_op_assemble_rgbd(const void* bgr_dev, const void* depth16_dev, int H, int W, int depth_clip, void* out_dev,
                           void* workspace_dev, void* stream);
 
+/* No-allocation variant of vipt_op_assemble_rgbd.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight
+ * serving loops, harnesses that forbid allocation).  Same inputs, outputs and results as vipt_op_assemble_rgbd, but the
+ * histogram scratch ((65536 + 4) * 4 = 262 160 bytes) is a file-scope `static __device__` array of the library: every
+ * GPU that loads the library holds it until exit; nothing is allocated or freed by the call (no cudaMalloc / cudaFree,
+ * no allocating library routine).  Limits: H * W <= VIPT_NOALLOC_MAX_PIXELS, otherwise VIPT_ERR_ARG with a message in
+ * vipt_last_error().  Every call on a GPU shares the one array (cleared at the start of each call): calls that overlap
+ * on the same GPU (different streams, no ordering) race; serialise them or use the workspace variant. */
+#define VIPT_NOALLOC_MAX_PIXELS (4096 * 4096)
+int vipt_op_assemble_rgbd_noalloc(const void* bgr_dev, const void* depth16_dev, int H, int W, int depth_clip,
+                                  void* out_dev, void* stream);
+
 /* ---- engine: the drop-in for ViPTTrack.initialize/track (ViPT/lib/test/tracker/vipt.py:41-110) and for
  * build_viptrack(...).forward(template, search, ce_template_mask) (ViPT/lib/models/vipt/ostrack_prompt.py:39-58),
  * batched over `batch` independent sequences ---- */

@@ -29,6 +29,7 @@ SIGNATURES = {
                                 c_i64, c_void_p, c_void_p]),
     "vipt_op_assemble_rgbx": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),
     "vipt_op_assemble_rgbd": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "vipt_op_assemble_rgbd_noalloc": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "vipt_engine_create": (c_int, [ctypes.POINTER(c_void_p)]),
     "vipt_engine_destroy": (c_int, [c_void_p]),
     "vipt_engine_set_tensor": (c_int, [c_void_p, ctypes.c_char_p, c_void_p, c_i64]),

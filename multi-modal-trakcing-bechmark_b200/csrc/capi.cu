@@ -76,6 +76,19 @@ int vipt_op_assemble_rgbd(const void* bgr_dev, const void* depth16_dev, int H, i
   return vipt::launch_assemble_rgbd(bgr_dev, depth16_dev, H, W, depth_clip, out_dev, workspace_dev, (cudaStream_t)stream);
 }
 
+int vipt_op_assemble_rgbd_noalloc(const void* bgr_dev, const void* depth16_dev, int H, int W, int depth_clip,
+                                  void* out_dev, void* stream) {
+  if (!bgr_dev || !depth16_dev || !out_dev || H < 1 || W < 1) { set_err("vipt_op_assemble_rgbd_noalloc: null pointer or empty image"); return VIPT_ERR_ARG; }
+  if ((long long)H * (long long)W > (long long)VIPT_NOALLOC_MAX_PIXELS) {
+    set_err("vipt_op_assemble_rgbd_noalloc: H * W exceeds VIPT_NOALLOC_MAX_PIXELS (16 777 216); use vipt_op_assemble_rgbd "
+            "with a caller-provided workspace");
+    return VIPT_ERR_ARG;
+  }
+  int r = vipt::launch_assemble_rgbd_noalloc(bgr_dev, depth16_dev, H, W, depth_clip, out_dev, (cudaStream_t)stream);
+  if (r) set_err("vipt_op_assemble_rgbd_noalloc: cudaGetSymbolAddress or launch failed");
+  return r;
+}
+
 // ---------------------------------------------------------------- engine
 int vipt_engine_create(void** out) {
   if (!out) return VIPT_ERR_ARG;

@@ -154,4 +154,30 @@ int launch_assemble_rgbd(const void* bgr, const void* depth16, int H, int W, int
   return cudaGetLastError() == cudaSuccess ? VIPT_OK : VIPT_ERR_LAUNCH;
 }
 
+// ------------------------------------------------------------------------------------------------
+// No-allocation variant of the 'rgbcolormap' assembly (vipt_op_assemble_rgbd_noalloc): the 65536-bin histogram + 4
+// parameter words live in a file-scope device array instead of a caller-provided workspace, for callers that cannot
+// call cudaMalloc (stream capture, tight serving loops, harnesses that forbid it).  262 160 bytes per GPU that loads
+// the library, held until exit.  In host code `g_rgbd_scratch` is only a host-side stand-in for the symbol, never a
+// device address: the address is asked for once per device, with that device current, and cached.
+// Every call shares the array and it keeps the last call's contents, so the histogram is cleared at the start of
+// each call; two calls that overlap on one GPU (different streams) race on it.
+// ------------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned int g_rgbd_scratch[65536 + 4];
+
+int launch_assemble_rgbd_noalloc(const void* bgr, const void* depth16, int H, int W, int depth_clip, void* out,
+                                 cudaStream_t st) {
+  constexpr int kMaxDevices = 64;
+  static unsigned int* scratch_of_device[kMaxDevices] = {};
+  if (H < 1 || W < 1 || (long long)H * (long long)W > (long long)VIPT_NOALLOC_MAX_PIXELS) return VIPT_ERR_ARG;
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return VIPT_ERR_LAUNCH;
+  if (!scratch_of_device[dev]) {            // set-up, once per device, with that device current
+    unsigned int* ptr = nullptr;
+    if (cudaGetSymbolAddress((void**)&ptr, g_rgbd_scratch) != cudaSuccess || !ptr) return VIPT_ERR_LAUNCH;
+    scratch_of_device[dev] = ptr;
+  }
+  return launch_assemble_rgbd(bgr, depth16, H, W, depth_clip, out, scratch_of_device[dev], st);
+}
+
 }  // namespace vipt

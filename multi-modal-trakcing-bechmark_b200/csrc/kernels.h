@@ -32,6 +32,8 @@ int launch_final_norm(const float* x, const void* delta, int n_cur, const int* s
                       void* feat16, float* feat32, int B, int lens_t, int lens_full, cudaStream_t st);
 
 int launch_assemble_rgbx(const void* bgr, const void* xbgr, int H, int W, void* out, cudaStream_t st);
+int launch_assemble_rgbd_noalloc(const void* bgr, const void* depth16, int H, int W, int depth_clip, void* out,
+                                 cudaStream_t st);      // scratch in a static __device__ array (frames.cu)
 int launch_assemble_rgbd(const void* bgr, const void* depth16, int H, int W, int depth_clip, void* out, void* workspace,
                          cudaStream_t st);
 
