@@ -344,15 +344,15 @@ def hbm_rooflines(prof, B, boxes, peaks, peak_src):
 
 def gemm_traffic(B, n_gemm):
     """dram__bytes_read.sum + dram__bytes_write.sum of the GEMM launches of one step, per launch, from the committed ncu
-    launch list (profiles/r1_gemm_traffic.json, written by scripts/launch_summary.py --json).  None when the batch of
+    launch list (profiles/r2_gemm_traffic.json, written by scripts/launch_summary.py --json).  None when the batch of
     this run differs from the profiled one."""
-    p = os.path.join(ROOT, "profiles", "r1_gemm_traffic.json")
+    p = os.path.join(ROOT, "profiles", "r2_gemm_traffic.json")
     try:
         j = json.load(open(p))
     except (OSError, ValueError):
-        return None, "no profiles/r1_gemm_traffic.json"
+        return None, "no profiles/r2_gemm_traffic.json"
     if j.get("batch") != B:
-        return None, "profiles/r1_gemm_traffic.json is for batch %s" % j.get("batch")
+        return None, "profiles/r2_gemm_traffic.json is for batch %s" % j.get("batch")
     steps = j.get("steps", 1)
     tot = sum(k["dram_read_bytes"] + k["dram_write_bytes"] for n, k in j["kernels"].items() if n.startswith("gemm"))
     n = sum(k["launches"] for name, k in j["kernels"].items() if name.startswith("gemm"))
