@@ -31,6 +31,19 @@ const char* vipt_last_error(void);
 int vipt_op_gemm(const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, int bn, int epi,
                  void* out, int64_t ldc, const float* bias, const float* resid, void* stream);
 
+/* LayerNorm folded into a GEMM pair (north star (b); ViPT/lib/models/layers/attn_blocks.py:94,103: x = x + proj(..);
+ * mlp(norm2(x))), 2-CTA kernel, N % 256 == 0.
+ * Producer: x (M,N) fp32 <- x + A W^T + bias in place, x16 (M,N) fp16 = the updated rows, stat_out (2*N/256, M, 2)
+ * fp32 = per-row (sum, sum of squares) of 128 columns each (part 2t + h: the 16-column groups h, h+2, .. of tile t). */
+int vipt_op_gemm_resid_stat(const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, float* x, void* x16,
+                            const float* bias, float* stat_out, void* stream);
+/* Consumer: out fp16 = [gelu](rstd * (A W^T - mean * colsum) + bias) with mean / rstd of every row of A (width K) from
+ * stat_in (stat_parts, M, 2); the caller passes W = fp16(gamma * W0), colsum = row sums of that fp16 W and
+ * bias = b0 + W0 beta, which makes this LayerNorm(x) W0^T + b0. */
+int vipt_op_gemm_lnfold(const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, int gelu, void* out,
+                        int64_t ldc, const float* bias, const float* colsum, const float* stat_in, int stat_parts, float eps,
+                        void* stream);
+
 /* Fused crop + zero pad + cv2-exact bilinear resize + /255, mean, std + patch-major store.  Replaces
  * sample_target (ViPT/lib/train/data/processing_utils.py:14-76) + PreprocessorMM.process
  * (ViPT/lib/test/tracker/data_utils.py:20-24).  frame_ptrs_dev: device array of B pointers to uint8

@@ -26,9 +26,32 @@ const char* vipt_last_error(void) { return g_err; }
 int vipt_op_gemm(const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, int bn, int epi,
                  void* out, int64_t ldc, const float* bias, const float* resid, void* stream) {
   vipt::GemmOp op;
-  int r = (bn == 512 || bn == 640) ? vipt::gemm2_plan(&op, A, lda, W, ldw, M, N, K, epi, out, ldc, bias, bn == 640 ? -1 : 0)
+  int r = (bn == 512 || bn == 640) ? vipt::gemm2_plan(&op, A, lda, W, ldw, M, N, K, epi, out, ldc, bias, bn == 640 ? -1 : num_sms() / 2)
                     : vipt::gemm_plan(&op, A, lda, 0, W, ldw, 0, 1, M, N, K, bn, epi, out, ldc, 0, 0, bias, resid);
   if (r) { set_err("gemm_plan failed"); return r; }
+  r = vipt::gemm_launch(op, num_sms(), (cudaStream_t)stream);
+  if (r) set_err(cudaGetErrorString(cudaGetLastError()));
+  return r;
+}
+
+int vipt_op_gemm_resid_stat(const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, float* x, void* x16,
+                            const float* bias, float* stat_out, void* stream) {
+  vipt::GemmOp op;
+  int r = vipt::gemm2_plan_resid_stat(&op, A, lda, W, ldw, M, N, K, x, x16, bias, (float2*)stat_out);
+  if (r) { set_err("gemm2_plan_resid_stat failed"); return r; }
+  r = vipt::gemm_launch(op, num_sms(), (cudaStream_t)stream);
+  if (r) set_err(cudaGetErrorString(cudaGetLastError()));
+  return r;
+}
+int vipt_op_gemm_lnfold(const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, int gelu, void* out,
+                        int64_t ldc, const float* bias, const float* colsum, const float* stat_in, int stat_parts, float eps,
+                        void* stream) {
+  if (!colsum || !stat_in || stat_parts < 1) return VIPT_ERR_ARG;
+  vipt::GemmOp op;
+  int r = vipt::gemm2_plan(&op, A, lda, W, ldw, M, N, K, gelu ? vipt::EPI_LNFOLD_GELU_F16 : vipt::EPI_LNFOLD_F16, out, ldc, bias,
+                             num_sms() / 2);
+  if (r) { set_err("gemm2_plan (LayerNorm fold) failed"); return r; }
+  vipt::gemm2_set_lnfold(&op, (const float2*)stat_in, stat_parts, colsum, eps);
   r = vipt::gemm_launch(op, num_sms(), (cudaStream_t)stream);
   if (r) set_err(cudaGetErrorString(cudaGetLastError()));
   return r;
@@ -95,6 +118,7 @@ int vipt_engine_create(void** out) {
   vipt::Engine* e = new vipt::Engine();
   e->opt_zero_copy = getenv("VIPT_NO_ZEROCOPY") == nullptr;
   e->opt_speculate = getenv("VIPT_NO_SPECULATION") == nullptr;
+  e->opt_lnfold = getenv("VIPT_NO_LNFOLD") == nullptr;
   *out = e;
   return VIPT_OK;
 }
@@ -190,6 +214,7 @@ int64_t vipt_engine_info(void* ev, const char* what) {
   if (!e || !what) return -1;
   if (!strcmp(what, "launches_per_step")) return e->launches_per_step;
   if (!strcmp(what, "batch")) return e->B;
+  if (!strcmp(what, "lnfold_layers")) { int n = 0; for (int i = 0; i < vipt::kDepth; ++i) n += e->L[i].fuse_ln2 + e->L[i].fuse_ln1; return n; }
   if (!strcmp(what, "final_tokens")) return e->n_tok[vipt::kDepth];
   if (!strncmp(what, "n_tok_", 6)) { int i = atoi(what + 6); return (i >= 0 && i <= vipt::kDepth) ? e->n_tok[i] : -1; }
   return -1;

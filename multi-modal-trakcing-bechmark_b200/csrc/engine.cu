@@ -114,6 +114,45 @@ void fold_conv_bn(Packer& pk, const std::string& p, int cout, int cin, float* w_
 
 }  // namespace
 
+// candidate-elimination schedule: CE_LOC = [3,6,9], keep ratio 0.7 (attn_blocks.py:40); and which LayerNorms travel
+// inside the GEMMs (gemm2.cu "LayerNorm fold"): only where both GEMMs of the pair run on the 2-CTA kernel (large
+// batches) and no candidate elimination sits between them
+void Engine::plan_schedule() {
+  int ns = kLensX;
+  for (int i = 0; i < kDepth; ++i) {
+    n_tok[i] = kLensT + ns;
+    ce_keep[i] = 0;
+    if (i == 3 || i == 6 || i == 9) {
+      ce_keep[i] = (int)ceil(0.7 * (double)ns);
+      ns = ce_keep[i];
+    }
+    n_mlp[i] = kLensT + ns;
+  }
+  n_tok[kDepth] = kLensT + ns;
+  for (int i = 0; i < kDepth; ++i) {
+    auto pair = [&](int n) { return ((B * n + 255) / 256) * 3 >= num_sms / 2; };
+    L[i].fuse_ln2 = opt_lnfold && !ce_keep[i] && pair(n_tok[i]);
+    L[i].fuse_ln1 = opt_lnfold && !deep && i >= 1 && pair(n_tok[i]);
+  }
+}
+
+// W (N, 768) row-major -> gamma * W; returns bias' = b + W beta and the column sums of the fp16-rounded rows
+static void fold_ln(const std::vector<float>& w, const std::vector<float>& b, const std::vector<float>& g,
+                    const std::vector<float>& be, int N, std::vector<float>& wf, std::vector<float>& bf, std::vector<float>& cs) {
+  wf.resize((size_t)N * 768); bf.resize(N); cs.resize(N);
+  for (int n = 0; n < N; ++n) {
+    double sb = b[n], sc = 0;
+    for (int k = 0; k < 768; ++k) {
+      const float v = w[(size_t)n * 768 + k] * g[k];
+      wf[(size_t)n * 768 + k] = v;
+      sc += (double)__half2float(__float2half_rn(v));
+      sb += (double)w[(size_t)n * 768 + k] * (double)be[k];
+    }
+    bf[n] = (float)sb;
+    cs[n] = (float)sc;
+  }
+}
+
 int Engine::finalize(int batch, bool deep_prompt) {
   if (finalized) return VIPT_ERR_STATE;
   B = batch;
@@ -121,6 +160,7 @@ int Engine::finalize(int batch, bool deep_prompt) {
   int dev = 0;
   CK(cudaGetDevice(&dev));
   CK(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
+  plan_schedule();
   Packer pk{this};
   const std::string bb = "backbone.";
   // ---- patch embeddings: group 0 = RGB (patch_embed), group 1 = X (patch_embed_prompt)
@@ -155,6 +195,21 @@ int Engine::finalize(int batch, bool deep_prompt) {
     L[i].ln1_b = pk.up_f32(pk.get(p + "norm1.bias", 768)->data(), 768);
     L[i].ln2_g = pk.up_f32(pk.get(p + "norm2.weight", 768)->data(), 768);
     L[i].ln2_b = pk.up_f32(pk.get(p + "norm2.bias", 768)->data(), 768);
+    std::vector<float> wf, bf, cs;
+    if (L[i].fuse_ln2) {
+      fold_ln(*pk.get(p + "mlp.fc1.weight", 3072 * 768), *pk.get(p + "mlp.fc1.bias", 3072), *pk.get(p + "norm2.weight", 768),
+              *pk.get(p + "norm2.bias", 768), 3072, wf, bf, cs);
+      L[i].w_fc1 = pk.up_f16(wf.data(), wf.size());      // (the plain copy above stays allocated, unused)
+      L[i].b_fc1 = pk.up_f32(bf.data(), bf.size());
+      L[i].cs_fc1 = pk.up_f32(cs.data(), cs.size());
+    }
+    if (L[i].fuse_ln1) {
+      fold_ln(*pk.get(p + "attn.qkv.weight", 2304 * 768), *pk.get(p + "attn.qkv.bias", 2304), *pk.get(p + "norm1.weight", 768),
+              *pk.get(p + "norm1.bias", 768), 2304, wf, bf, cs);
+      L[i].w_qkv = pk.up_f16(wf.data(), wf.size());
+      L[i].b_qkv = pk.up_f32(bf.data(), bf.size());
+      L[i].cs_qkv = pk.up_f32(cs.data(), cs.size());
+    }
   }
   norm_g = pk.up_f32(pk.get(bb + "norm.weight", 768)->data(), 768);
   norm_b = pk.up_f32(pk.get(bb + "norm.bias", 768)->data(), 768);

@@ -24,6 +24,11 @@ struct LayerW {
   __half *w_qkv, *w_proj, *w_fc1, *w_fc2;
   float *b_qkv, *b_proj, *b_fc1, *b_fc2;
   float *ln1_g, *ln1_b, *ln2_g, *ln2_b;
+  // LayerNorm fold (gemm2.cu): when fuse_ln2 / fuse_ln1 is set, w_fc1 / w_qkv hold fp16(gamma * W), b_* hold
+  // b + W beta and cs_* the column sums of the fp16 weight rows
+  float *cs_fc1 = nullptr, *cs_qkv = nullptr;
+  bool fuse_ln2 = false;     // norm2 folded into attn.proj (residual + statistics) and mlp.fc1
+  bool fuse_ln1 = false;     // shallow prompt only: norm1 folded into the previous block's mlp.fc2 and attn.qkv
 };
 struct PromptW {
   float *wg_a, *wg_d, *sc, *w1, *b1;
@@ -58,6 +63,7 @@ struct Engine {
   // activations
   __half *apatch, *xn, *dbuf, *qkv, *att, *hbuf, *feat16, *h1, *h2, *h3, *h4;
   float *E, *xA, *xB, *XD, *FV, *ce_prob, *ce_score, *feat32;
+  float2* lnstat = nullptr;           // LayerNorm fold: (6, B * 320) partial (sum, sum of squares) per row
   int *giA, *giB, *perm, *removed, *slot_of_pos, *ident, *err;
   // outputs / state
   float *score_map, *size_map, *offset_map, *pred_boxes, *out_scores;
@@ -90,6 +96,9 @@ struct Engine {
   // VIPT_NO_ZEROCOPY=1 uploads page-locked frames with per-sequence 2-D copies instead of the gather kernel,
   // VIPT_NO_SPECULATION=1 disables the copy-engine upload next to the running step.  Both covered by tests.
   bool opt_zero_copy = true, opt_speculate = true;
+  // VIPT_NO_LNFOLD=1 keeps every LayerNorm a separate pass (ln_rows_kernel); read once at engine creation, covered by a test
+  bool opt_lnfold = true;
+  void plan_schedule();                    // CE schedule + which LayerNorms are folded (needs B, deep, num_sms)
   // zero-copy gather: the device-visible addresses of the B host frames travel as a kernel parameter
   static constexpr int kRoiSlots = 4;      // steps that may be enqueued before their results are collected
   static constexpr int kRoiMaxB = 128;

@@ -36,18 +36,6 @@ void Engine::prof_end(cudaStream_t st) {
 }
 
 int Engine::finalize_buffers() {
-  // candidate-elimination schedule: CE_LOC = [3,6,9], keep ratio 0.7 (attn_blocks.py:40)
-  int ns = kLensX;
-  for (int i = 0; i < kDepth; ++i) {
-    n_tok[i] = kLensT + ns;
-    ce_keep[i] = 0;
-    if (i == 3 || i == 6 || i == 9) {
-      ce_keep[i] = (int)ceil(0.7 * (double)ns);
-      ns = ce_keep[i];
-    }
-    n_mlp[i] = kLensT + ns;
-  }
-  n_tok[kDepth] = kLensT + ns;
   const size_t R = (size_t)B * kLensFull;
   const size_t RH = (size_t)B * kLensX;
 #define AL(ptr, type, count)                          \
@@ -58,7 +46,7 @@ int Engine::finalize_buffers() {
   AL(apatch, __half, 2 * R * 768);
   AL(E, float, 2 * R * 768);
   AL(xA, float, R * 768); AL(xB, float, R * 768);
-  AL(XD, float, R * 16); AL(FV, float, R * 8);
+  AL(XD, float, R * 16); AL(FV, float, R * 8); AL(lnstat, float2, 6 * R);
   AL(xn, __half, R * 768); AL(dbuf, __half, R * 768); AL(qkv, __half, R * 2304); AL(att, __half, R * 768); AL(hbuf, __half, R * 3072);
   AL(ce_prob, float, (size_t)B * kHeads * kLensX); AL(ce_score, float, 3 * RH);
   AL(feat16, __half, RH * 768); AL(feat32, float, R * 768);
@@ -114,15 +102,35 @@ int Engine::finalize_buffers() {
     }
     return gemm_plan(op, A, lda, 0, W, K, 0, 1, M, N, K, bn, epi, out, N, 0, 0, bias, nullptr);
   };
+  float* x_cur = xA;            // the residual stream ping-pongs between xA and xB at every candidate elimination
+  float* x_oth = xB;
   for (int i = 0; i < kDepth; ++i) {
     const int Ma = B * n_tok[i], Mm = B * n_mlp[i];
-    RET(plan_lin(&g_qkv[i], xn, 768, L[i].w_qkv, Ma, 2304, 768, EPI_BIAS_F16, qkv, L[i].b_qkv));
+    // LayerNorm fold (gemm2.cu): the producer GEMM adds its branch to x in place and leaves x16 (in xn) + row statistics,
+    // the consumer GEMM applies mean / rstd in its epilogue
+    if (L[i].fuse_ln1) {
+      RET(gemm2_plan(&g_qkv[i], xn, 768, L[i].w_qkv, 768, Ma, 2304, 768, EPI_LNFOLD_F16, qkv, 2304, L[i].b_qkv, num_sms / 2));
+      gemm2_set_lnfold(&g_qkv[i], lnstat, 6, L[i].cs_qkv, 1e-6f);
+    } else {
+      RET(plan_lin(&g_qkv[i], xn, 768, L[i].w_qkv, Ma, 2304, 768, EPI_BIAS_F16, qkv, L[i].b_qkv));
+    }
     RET(attention_plan(&a_op[i], qkv, B, n_tok[i]));
-    // proj / fc2 write their branch output as fp16 (dbuf); the residual add is fused into the next
+    // otherwise proj / fc2 write their branch output as fp16 (dbuf); the residual add is fused into the next
     // LayerNorm / prompt kernel, where it is coalesced
-    RET(plan_lin(&g_proj[i], att, 768, L[i].w_proj, Ma, 768, 768, EPI_BIAS_F16, dbuf, L[i].b_proj));
-    RET(plan_lin(&g_fc1[i], xn, 768, L[i].w_fc1, Mm, 3072, 768, EPI_GELU_F16, hbuf, L[i].b_fc1));
-    RET(plan_lin(&g_fc2[i], hbuf, 3072, L[i].w_fc2, Mm, 768, 3072, EPI_BIAS_F16, dbuf, L[i].b_fc2));
+    if (L[i].fuse_ln2) {
+      RET(gemm2_plan_resid_stat(&g_proj[i], att, 768, L[i].w_proj, 768, Ma, 768, 768, x_cur, xn, L[i].b_proj, lnstat));
+      RET(gemm2_plan(&g_fc1[i], xn, 768, L[i].w_fc1, 768, Mm, 3072, 768, EPI_LNFOLD_GELU_F16, hbuf, 3072, L[i].b_fc1, num_sms / 2));
+      gemm2_set_lnfold(&g_fc1[i], lnstat, 6, L[i].cs_fc1, 1e-6f);
+    } else {
+      RET(plan_lin(&g_proj[i], att, 768, L[i].w_proj, Ma, 768, 768, EPI_BIAS_F16, dbuf, L[i].b_proj));
+      RET(plan_lin(&g_fc1[i], xn, 768, L[i].w_fc1, Mm, 3072, 768, EPI_GELU_F16, hbuf, L[i].b_fc1));
+    }
+    if (ce_keep[i]) { float* t = x_cur; x_cur = x_oth; x_oth = t; }
+    if (i + 1 < kDepth && L[i + 1].fuse_ln1) {
+      RET(gemm2_plan_resid_stat(&g_fc2[i], hbuf, 3072, L[i].w_fc2, 3072, Mm, 768, 3072, x_cur, xn, L[i].b_fc2, lnstat));
+    } else {
+      RET(plan_lin(&g_fc2[i], hbuf, 3072, L[i].w_fc2, Mm, 768, 3072, EPI_BIAS_F16, dbuf, L[i].b_fc2));
+    }
   }
   const int MH = B * kLensX;
   // center head: implicit 3x3 convolutions (no im2col buffer); BN folded, ReLU fused, towers grouped
@@ -195,7 +203,7 @@ int Engine::run_backbone_head(bool tracking, bool want_feat32, int debug_stop, c
         // cooperative persistent kernel (prompt_coop.cu)
         LAUNCH(K_PROMPT, launch_prompt_coop(x, dbuf, n, gi, FV, XD, PW[i].wg_a, PW[i].fold, PW[i].w1t, PW[i].b1,
                                             L[i].ln1_g, L[i].ln1_b, xn, B, kLensT, kLensFull, num_sms, st));
-      } else {
+      } else if (!L[i].fuse_ln1) {
         LAUNCH(K_NORM, launch_ln_rows(x, n, dbuf, nullptr, 0, x, xn, L[i].ln1_g, L[i].ln1_b, B, n, kLensT, st));
       }
     }
@@ -214,7 +222,7 @@ int Engine::run_backbone_head(bool tracking, bool want_feat32, int debug_stop, c
       float* t = x; x = x_other; x_other = t;
       int* tg = gi; gi = gi_other; gi_other = tg == ident ? giB : tg;      // the identity array is never a destination
       ++ce_idx;
-    } else {
+    } else if (!L[i].fuse_ln2) {
       LAUNCH(K_NORM, launch_ln_rows(x, n, dbuf, nullptr, 0, x, xn, L[i].ln2_g, L[i].ln2_b, B, nm, kLensT, st));
     }
     STAGE_END();   // 7 + 7i: x after CE, xn = LN2(x)

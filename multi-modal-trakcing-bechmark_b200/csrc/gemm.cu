@@ -241,7 +241,15 @@ static EncodeTiledFn get_encode() {
 }
 
 static int make_tmap_dt(CUtensorMap* out, CUtensorMapDataType dt, const void* base, int rank, const uint64_t* dims,
-                        const uint64_t* strides_bytes, const uint32_t* box);
+                        const uint64_t* strides_bytes, const uint32_t* box, CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_128B);
+int make_tmap_ex(CUtensorMap* out, int dtype_f32, int swizzle_bytes, const void* base, int rank, const uint64_t* dims,
+                 const uint64_t* strides_bytes, const uint32_t* box) {
+  const CUtensorMapSwizzle swz = swizzle_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
+                                 : swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
+                                 : swizzle_bytes == 32 ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_NONE;
+  return make_tmap_dt(out, dtype_f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, base, rank, dims,
+                      strides_bytes, box, swz);
+}
 int make_tmap_f16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                   const uint32_t* box) {
   return make_tmap_dt(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, base, rank, dims, strides_bytes, box);
@@ -251,7 +259,7 @@ int make_tmap_f32(CUtensorMap* out, const void* base, int rank, const uint64_t* 
   return make_tmap_dt(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, base, rank, dims, strides_bytes, box);
 }
 static int make_tmap_dt(CUtensorMap* out, CUtensorMapDataType dt, const void* base, int rank, const uint64_t* dims,
-                        const uint64_t* strides_bytes, const uint32_t* box) {
+                        const uint64_t* strides_bytes, const uint32_t* box, CUtensorMapSwizzle swz) {
   EncodeTiledFn enc = get_encode();
   if (!enc) return VIPT_ERR_DRIVER;
   cuuint64_t d[5], st[4];
@@ -259,7 +267,7 @@ static int make_tmap_dt(CUtensorMap* out, CUtensorMapDataType dt, const void* ba
   for (int i = 0; i < rank; ++i) { d[i] = dims[i]; b[i] = box[i]; es[i] = 1; }
   for (int i = 0; i + 1 < rank; ++i) st[i] = strides_bytes[i];
   CUresult r = enc(out, dt, (cuuint32_t)rank, const_cast<void*>(base), d, st, b, es,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     fprintf(stderr, "vipt: cuTensorMapEncodeTiled failed (%d) rank=%d dims=%llu,%llu box=%u,%u\n", (int)r, rank,
@@ -313,7 +321,7 @@ int gemm_launch(const GemmOp& op, int num_sms, cudaStream_t st) {
 static int plan_common(GemmOp* op, const void* W, int64_t ldw, int64_t w_group_stride, int G, int M, int N, int K, int bn,
                        int epi, void* out, int64_t ldc, int64_t out_group_stride, int64_t out_group_col, const float* bias,
                        const float* resid) {
-  if (K % BK != 0 || N % bn != 0 || (bn != 256 && bn != 128 && bn != 64 && bn != 32) || M <= 0 || G <= 0)
+  if (K % BK != 0 || N % bn != 0 || (bn != 256 && bn != 128 && bn != 64 && bn != 32) || M <= 0 || G <= 0 || epi > EPI_RESID_F32)
     return VIPT_ERR_ARG;
   if ((ldw * 2) % 16 != 0 || (reinterpret_cast<uintptr_t>(W) & 15)) return VIPT_ERR_ARG;
   uint64_t db[3] = {(uint64_t)K, (uint64_t)N, (uint64_t)G};
@@ -325,6 +333,8 @@ static int plan_common(GemmOp* op, const void* W, int64_t ldw, int64_t w_group_s
   op->p.out = out; op->p.ldc = ldc; op->p.out_group_stride = out_group_stride; op->p.out_group_col = out_group_col;
   op->p.bias = bias; op->p.resid = resid;
   op->p.conv_cb_per_tap = 0; op->p.conv_cin_stride = 0;
+  op->p.stat_out = nullptr; op->p.stat_in = nullptr; op->p.stat_parts = 0; op->p.colsum = nullptr; op->p.ln_eps = 0.f;
+  op->p.tail_from = 0; op->p.tail_split = 1;
   op->bn = bn; op->epi = epi;
   return VIPT_OK;
 }

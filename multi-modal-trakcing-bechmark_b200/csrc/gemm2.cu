@@ -12,6 +12,20 @@
 //   empty[s]  (each CTA) : tcgen05.commit multicast from the leader's MMA thread
 //   tfull[a]  (each CTA) : tcgen05.commit multicast after the last k-block
 //   tempty[a] (leader)   : 4 epilogue warps of each CTA arrive (peer: remote arrive through mapa)
+//
+// LayerNorm fold (north star (b): "GEMMs ... with LayerNorm, GELU and bias fused in"; reference sites
+// ViPT/lib/models/layers/attn_blocks.py:94,103).  blocks[i].norm2 between attn.proj and mlp.fc1 (and, without deep
+// prompts, norm1 between mlp.fc2 and the next attn.qkv) is not a pass over the residual stream any more:
+//   producer  EPI_RESID_STAT   x <- x + acc + bias  in fp32, IN PLACE through one fp32 tensor map (a fourth warp
+//             streams the x slabs of the tile in through a 3-deep ring while the main loop runs; the epilogue adds,
+//             writes the fp32 slab and an fp16 copy x16 back with TMA stores) and every thread -- it owns one row of
+//             the tile -- keeps (sum, sum of squares) of its 128 columns: stat[(2 tile_n + half)][row]
+//   consumer  EPI_LNFOLD_*     A = x16, W' = fp16(gamma * W):   LN(x) W^T + b = rstd (x16 W'^T - mean colsum(W')) + (b + W beta)
+//             mean / rstd per row from the partial sums (per thread: its row), two FMAs per element
+// The fp16 rounding of x instead of LN(x) gives the same operand error as long as |mean| is not large against the
+// standard deviation of a row (measured on the synthetic weight sets: 2.9e-4 relative either way).
+#include <stdlib.h>
+
 #include "gemm.h"
 #include "sm100_ptx.cuh"
 
@@ -27,13 +41,19 @@ constexpr int kThreads = 384;          // warp 0 TMA, 1 MMA, 2 TMEM alloc, 4..11
 constexpr int kEpiThreads = 256;
 // BN = columns per pair tile: 256, or 128 for the N = 768 layers (proj, fc2), whose 3 x tiles_m grid of
 // 256-wide tiles leaves the last wave of the persistent loop a third empty
-template <int BN>
+constexpr int kResidRing = 3;      // EPI_RESID_STAT: fp32 slabs of x in flight towards the epilogue
+template <int BN, int EPI>
 struct Cfg {
-  static constexpr int kStages = BN == 256 ? 5 : 6;
+  static constexpr bool kResid = EPI == EPI_RESID_STAT;
+  static constexpr int kStages = kResid ? 4 : (BN == 256 ? 5 : 6);
   static constexpr int kBBytes = (BN / 2) * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  // 4 staging slabs: 2 for fp16 outputs (double-buffered 64-column slabs), 4 for fp32 outputs (two 32-column slabs per step)
-  static constexpr int kSmemBytes = 1024 + kStages * kStageBytes + 4 * kSlabBytes + BN * 4 + (2 * kStages + 4) * 8 + 16;
+  // 4 staging slabs: 2 for fp16 outputs (double-buffered 64-column slabs; the LayerNorm-fold consumers keep the column
+  // sums in the third), 4 for fp32 outputs (two 32-column slabs per step).  EPI_RESID_STAT: 3 fp32 slabs in (128 rows x
+  // 32 columns), 2 fp32 slabs out, 2 half-size fp16 slabs out.
+  static constexpr int kSlabs = kResid ? kResidRing + 3 : 4;
+  static constexpr int kSmemBytes =
+      1024 + kStages * kStageBytes + kSlabs * kSlabBytes + BN * 4 + (2 * kStages + 4 + 2 * kResidRing) * 8 + 16;
 };
 }  // namespace g2
 
@@ -88,22 +108,39 @@ __device__ __forceinline__ void umma_commit_2cta(uint64_t* bar) {     // arrives
       : "memory");
 }
 
+// TMEM -> registers: this warp's 32 lanes x 16 consecutive fp32 columns
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr)
+      : "memory");
+}
+
 template <int EPI, int BN>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(g2::kThreads, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-             const __grid_constant__ CUtensorMap tmC, GemmParams p) {
+             const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmC2,
+             const __grid_constant__ CUtensorMap tmB2, GemmParams p) {
   using namespace g2;
-  constexpr int kStages = Cfg<BN>::kStages, kStageBytes = Cfg<BN>::kStageBytes;
+  constexpr int kStages = Cfg<BN, EPI>::kStages, kStageBytes = Cfg<BN, EPI>::kStageBytes;
+  constexpr bool kResid = EPI == EPI_RESID_STAT;
+  constexpr bool kFold = EPI == EPI_LNFOLD_F16 || EPI == EPI_LNFOLD_GELU_F16;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* tiles = smem;
   uint8_t* slab = smem + kStages * kStageBytes;            // 2 x 16 KB output staging (TMA store source)
-  float* bias_s = reinterpret_cast<float*>(slab + 4 * kSlabBytes);
+  float* bias_s = reinterpret_cast<float*>(slab + Cfg<BN, EPI>::kSlabs * kSlabBytes);
+  float* cs_s = reinterpret_cast<float*>(slab + 2 * kSlabBytes);      // kFold: column sums (fp16 outputs use 2 slabs)
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(bias_s + BN);
   uint64_t* empty_bar = full_bar + kStages;
   uint64_t* tfull_bar = empty_bar + kStages;
   uint64_t* tempty_bar = tfull_bar + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  uint64_t* rfull_bar = tempty_bar + 2;                               // kResid: x slab ring
+  uint64_t* rempty_bar = rfull_bar + kResidRing;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(rempty_bar + kResidRing);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -113,13 +150,33 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   const int num_clusters = gridDim.x >> 1;
   const int tiles_m = (p.M + 2 * BM - 1) / (2 * BM);
   const int tiles_n = p.N / BN;
-  const int num_tiles = tiles_m * tiles_n;
+  // Work units: the tiles of the complete rounds of the persistent loop, then the tiles of the last, partial round
+  // cut into tail_split column strips (unit u >= tail_from: tile tail_from + (u - tail_from) / split, strip
+  // (u - tail_from) % split).  Strips use the same k order, so results do not depend on the split.
+  const int num_tiles = p.tail_from + (tiles_m * tiles_n - p.tail_from) * p.tail_split;
   const int num_kb = p.K / BK;
+  struct Unit { int tm, n0, width; };
+  auto unit_of = [&](int u) -> Unit {
+    int tile = u, strip = 0, width = BN;
+    if (u >= p.tail_from) {
+      const int v = u - p.tail_from;
+      tile = p.tail_from + v / p.tail_split;
+      strip = v % p.tail_split;
+      width = BN / p.tail_split;
+    }
+    return Unit{tile / tiles_n, (tile % tiles_n) * BN + strip * width, width};
+  };
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
     tma_prefetch_desc(&tmC);
+    if (kResid) tma_prefetch_desc(&tmC2);
+    if (p.tail_split > 1) tma_prefetch_desc(&tmB2);
+    for (int s = 0; s < kResidRing; ++s) {
+      mbar_init(&rfull_bar[s], 1);
+      mbar_init(&rempty_bar[s], 8);   // 8 epilogue warps
+    }
     for (int s = 0; s < kStages; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
@@ -149,22 +206,24 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     int s = 0;
     uint32_t ph = 0;
     for (int t = cluster_id; t < num_tiles; t += num_clusters) {
-      const int tn = t % tiles_n;
-      const int tm = t / tiles_n;
+      const Unit un = unit_of(t);
+      const int tm = un.tm;
+      const bool strip = un.width != BN;
+      const uint32_t tx_bytes = 2 * (kABytes + (un.width / 2) * BK * 2);
       for (int kb = 0; kb < num_kb; ++kb) {
         mbar_wait(&empty_bar[s], ph ^ 1);
         uint8_t* a_dst = tiles + s * kStageBytes;
         uint8_t* b_dst = a_dst + kABytes;
         const uint32_t bar = mapa_cta(smem_u32(&full_bar[s]), 0);
         if (elect_one()) {
-          if (leader) mbar_expect_tx(&full_bar[s], 2 * kStageBytes);
+          if (leader) mbar_expect_tx(&full_bar[s], tx_bytes);
           if (p.conv_cb_per_tap) {    // implicit 3x3 conv: the pair tile is one sequence's 16 x 16 map, 8 rows per CTA
             const int tap = kb / p.conv_cb_per_tap, cb = kb % p.conv_cb_per_tap;
             tma_load_4d_2cta(a_dst, &tmA, bar, cb * BK, tap % 3 - 1, (int)rank * 8 + tap / 3 - 1, tm);
           } else {
             tma_load_3d_2cta(a_dst, &tmA, bar, kb * BK, tm * 2 * BM + (int)rank * BM, 0);
           }
-          tma_load_3d_2cta(b_dst, &tmB, bar, kb * BK, tn * BN + (int)rank * (BN / 2), 0);
+          tma_load_3d_2cta(b_dst, strip ? &tmB2 : &tmB, bar, kb * BK, un.n0 + (int)rank * (un.width / 2), 0);
         }
         __syncwarp();
         if (++s == kStages) { s = 0; ph ^= 1; }
@@ -174,12 +233,12 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     // ------------------------------------------------ MMA issuer (leader CTA only).  The whole warp runs the loop so
     // that barriers, stage indices and descriptors stay warp-uniform (uniform registers feed UTCHMMA directly; a
     // single divergent thread made the compiler wrap every MMA in an R2UR broadcast loop); one elected lane issues.
-    constexpr uint32_t idesc = make_idesc(2 * BM, BN);
     int s = 0;
     uint32_t ph = 0;
     int as = 0;
     uint32_t aph = 0;
     for (int t = cluster_id; t < num_tiles; t += num_clusters) {
+      const uint32_t idesc = make_idesc(2 * BM, t >= p.tail_from ? BN / p.tail_split : BN);
       mbar_wait(&tempty_bar[as], aph ^ 1);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + as * BN;
@@ -201,6 +260,24 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
       __syncwarp();
       if (++as == 2) { as = 0; aph ^= 1; }
     }
+  } else if (kResid && warp == 3) {
+    // ------------------------------------------------ x slab producer (both CTAs): the fp32 rows this CTA's tile updates,
+    // 32 columns at a time, in the order the epilogue consumes them; runs ahead of the epilogue by the ring depth
+    int rs = 0;
+    uint32_t rph = 0;
+    for (int t = cluster_id; t < num_tiles; t += num_clusters) {
+      const int n0 = (t % tiles_n) * BN;          // (no column strips with this epilogue: gemm2_plan_resid_stat)
+      const int row0 = (t / tiles_n) * 2 * BM + (int)rank * BM;
+      for (int j = 0; j < BN / 32; ++j) {
+        mbar_wait(&rempty_bar[rs], rph ^ 1);
+        if (elect_one()) {
+          mbar_expect_tx(&rfull_bar[rs], kSlabBytes);
+          tma_load_3d(slab + rs * kSlabBytes, &tmC, &rfull_bar[rs], n0 + j * 32, row0, 0);
+        }
+        __syncwarp();
+        if (++rs == kResidRing) { rs = 0; rph ^= 1; }
+      }
+    }
   } else if (warp >= 4) {
     // ------------------------------------------------ epilogue (both CTAs, own 128 rows)
     const int we = (warp - 4) & 3;           // TMEM lane group (warp % 4)
@@ -209,36 +286,134 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     const uint32_t bias_u32 = smem_u32(bias_s);
     int as = 0;
     uint32_t aph = 0;
+    int rs = 0;                  // kResid: x slab ring position
+    uint32_t rph = 0;
     for (int t = cluster_id; t < num_tiles; t += num_clusters) {
-      const int tn = t % tiles_n;
-      const int tm = t / tiles_n;
-      const int n0 = tn * BN;
+      const Unit un = unit_of(t);
+      const int tm = un.tm;
+      const int n0 = un.n0;
+      const int tn = n0 / BN;
+      const int n_slabs = un.width / kSlabCols;
+      const int row0 = tm * 2 * BM + (int)rank * BM;           // first row of this CTA's 128 x 256 tile
+      const int r = we * 32 + lane;                            // row within the tile == TMEM lane
       // (bias_s of the previous tile was last read before that tile's final slab barrier)
-      for (int i = et; i < BN; i += kEpiThreads) bias_s[i] = p.bias ? p.bias[n0 + i] : 0.f;
+      for (int i = et; i < un.width; i += kEpiThreads) bias_s[i] = p.bias ? p.bias[n0 + i] : 0.f;
+      float ln_rs = 0.f, ln_nm = 0.f;                          // kFold: rstd and -mean * rstd of this thread's row
+      if (kFold) {
+        for (int i = et; i < un.width; i += kEpiThreads) cs_s[i] = p.colsum[n0 + i];
+        if (row0 + r < p.M) {
+          float s1 = 0.f, s2 = 0.f;
+          for (int q = 0; q < p.stat_parts; ++q) {             // fixed order: results do not depend on the schedule
+            const float2 st = p.stat_in[(size_t)q * p.M + row0 + r];
+            s1 += st.x;
+            s2 += st.y;
+          }
+          const float inv_k = 1.f / (float)p.K;
+          const float mean = s1 * inv_k;
+          ln_rs = rsqrtf(fmaxf(fmaf(-mean, mean, s2 * inv_k), 0.f) + p.ln_eps);
+          ln_nm = -mean * ln_rs;
+        }
+      }
       asm volatile("bar.sync 1, 256;" ::: "memory");
       mbar_wait(&tfull_bar[as], aph);
       tc_fence_after();
-      const int row0 = tm * 2 * BM + (int)rank * BM;           // first row of this CTA's 128 x 256 tile
-      const int r = we * 32 + lane;                            // row within the tile == TMEM lane
+      if constexpr (kResid) {
+        // x <- x + acc + bias, 32 columns per step: this warp set's threads take 16 of them (hh)
+        const uint32_t taddr0 = tmem_base + as * BN + hh * 16 + ((uint32_t)(we * 32) << 16);
+        float s1 = 0.f, s2 = 0.f;
+        uint32_t v[16];
+        tmem_ld16(taddr0, v);
+#pragma unroll 1
+        for (int j = 0; j < BN / 32; ++j) {
+          mbar_wait(&rfull_bar[rs], rph);
+          const uint32_t in_row = smem_u32(slab + rs * kSlabBytes) + r * 128;
+          const uint32_t brow = bias_u32 + (j * 32 + hh * 16) * 4;
+          float f[16];
+          tmem_ld_wait();
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const float4 xq = lds128f(in_row + (((hh * 4 + q) ^ (r & 7)) * 16));
+            const float4 bq = lds128f(brow + q * 16);
+            f[q * 4 + 0] = (__uint_as_float(v[q * 4 + 0]) + bq.x) + xq.x;
+            f[q * 4 + 1] = (__uint_as_float(v[q * 4 + 1]) + bq.y) + xq.y;
+            f[q * 4 + 2] = (__uint_as_float(v[q * 4 + 2]) + bq.z) + xq.z;
+            f[q * 4 + 3] = (__uint_as_float(v[q * 4 + 3]) + bq.w) + xq.w;
+          }
+          if (j + 1 < BN / 32) tmem_ld16(taddr0 + (j + 1) * 32, v);
+#pragma unroll
+          for (int k = 0; k < 16; ++k) {
+            s1 += f[k];
+            s2 = fmaf(f[k], f[k], s2);
+          }
+          const uint32_t o32 = smem_u32(slab + (kResidRing + (j & 1)) * kSlabBytes) + r * 128;
+#pragma unroll
+          for (int q = 0; q < 4; ++q)
+            sts128(o32 + (((hh * 4 + q) ^ (r & 7)) * 16), __float_as_uint(f[q * 4 + 0]), __float_as_uint(f[q * 4 + 1]),
+                   __float_as_uint(f[q * 4 + 2]), __float_as_uint(f[q * 4 + 3]));
+          // fp16 copy: 128 rows x 32 columns = 64-byte rows, 64-byte swizzle (16-byte chunk ^= (row / 2) % 4)
+          const uint32_t o16 = smem_u32(slab + (kResidRing + 2) * kSlabBytes) + (j & 1) * (kSlabBytes / 2) + r * 64;
+#pragma unroll
+          for (int q = 0; q < 2; ++q)
+            sts128(o16 + (((hh * 2 + q) ^ ((r >> 1) & 3)) * 16), pack_op2(f[q * 8 + 0], f[q * 8 + 1]),
+                   pack_op2(f[q * 8 + 2], f[q * 8 + 3]), pack_op2(f[q * 8 + 4], f[q * 8 + 5]), pack_op2(f[q * 8 + 6], f[q * 8 + 7]));
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&rempty_bar[rs]);         // the x slab is consumed
+          if (++rs == kResidRing) { rs = 0; rph ^= 1; }
+          if (et == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+          asm volatile("bar.sync 1, 256;" ::: "memory");
+          if (et == 0) {
+            asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+                         ::"l"(reinterpret_cast<uint64_t>(&tmC)), "r"(smem_u32(slab + (kResidRing + (j & 1)) * kSlabBytes)),
+                           "r"(n0 + j * 32), "r"(row0), "r"(0)
+                         : "memory");
+            asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+                         ::"l"(reinterpret_cast<uint64_t>(&tmC2)),
+                           "r"(smem_u32(slab + (kResidRing + 2) * kSlabBytes) + (j & 1) * (kSlabBytes / 2)), "r"(n0 + j * 32),
+                           "r"(row0), "r"(0)
+                         : "memory");
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          }
+        }
+        if (row0 + r < p.M) p.stat_out[(size_t)(tn * 2 + hh) * p.M + row0 + r] = make_float2(s1, s2);
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(mapa_cta(smem_u32(&tempty_bar[as]), 0));
+        if (++as == 2) { as = 0; aph ^= 1; }
+        continue;
+      }
       const uint32_t taddr0 = tmem_base + as * BN + hh * 32 + ((uint32_t)(we * 32) << 16);
       uint32_t v[32];
       tmem_ld32(taddr0, v);
 #pragma unroll 1
-      for (int sl = 0; sl < BN / kSlabCols; ++sl) {
+      for (int sl = 0; sl < n_slabs; ++sl) {
         // fp16 outputs: one 64-column slab per step; fp32 outputs: each warp set fills its own 32-column slab
         uint8_t* buf = slab + (EPI == EPI_BIAS_F32 ? ((sl & 1) * 2 + hh) : (sl & 1)) * kSlabBytes;
         const uint32_t prow = smem_u32(buf) + r * 128;
         const uint32_t brow = bias_u32 + (sl * kSlabCols + hh * 32) * 4;
         float f[32];
         tmem_ld_wait();
+        if (kFold) {
+          const uint32_t crow = smem_u32(cs_s) + (sl * kSlabCols + hh * 32) * 4;
 #pragma unroll
-        for (int j = 0; j < 32; j += 4) {
-          const float4 bq = lds128f(brow + j * 4);
-          f[j] = __uint_as_float(v[j]) + bq.x; f[j + 1] = __uint_as_float(v[j + 1]) + bq.y;
-          f[j + 2] = __uint_as_float(v[j + 2]) + bq.z; f[j + 3] = __uint_as_float(v[j + 3]) + bq.w;
+          for (int j = 0; j < 32; j += 4) {
+            const float4 bq = lds128f(brow + j * 4);
+            const float4 cq = lds128f(crow + j * 4);
+            f[j] = fmaf(ln_rs, __uint_as_float(v[j]), fmaf(ln_nm, cq.x, bq.x));
+            f[j + 1] = fmaf(ln_rs, __uint_as_float(v[j + 1]), fmaf(ln_nm, cq.y, bq.y));
+            f[j + 2] = fmaf(ln_rs, __uint_as_float(v[j + 2]), fmaf(ln_nm, cq.z, bq.z));
+            f[j + 3] = fmaf(ln_rs, __uint_as_float(v[j + 3]), fmaf(ln_nm, cq.w, bq.w));
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            const float4 bq = lds128f(brow + j * 4);
+            f[j] = __uint_as_float(v[j]) + bq.x; f[j + 1] = __uint_as_float(v[j + 1]) + bq.y;
+            f[j + 2] = __uint_as_float(v[j + 2]) + bq.z; f[j + 3] = __uint_as_float(v[j + 3]) + bq.w;
+          }
         }
-        if (sl + 1 < BN / kSlabCols) tmem_ld32(taddr0 + (sl + 1) * kSlabCols, v);     // in flight during the math below
-        if (EPI == EPI_GELU_F16) {
+        if (sl + 1 < n_slabs) tmem_ld32(taddr0 + (sl + 1) * kSlabCols, v);     // in flight during the math below
+        if (EPI == EPI_GELU_F16 || EPI == EPI_LNFOLD_GELU_F16) {
 #pragma unroll
           for (int j = 0; j < 32; j += 2) gelu_erf2x2(f[j], f[j + 1]);
         }
@@ -302,16 +477,17 @@ template <int EPI, int BN>
 static int launch2_t(const GemmOp& op, int num_sms, cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
-    if (cudaFuncSetAttribute(gemm2_kernel<EPI, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, g2::Cfg<BN>::kSmemBytes) !=
-        cudaSuccess)
+    if (cudaFuncSetAttribute(gemm2_kernel<EPI, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             g2::Cfg<BN, EPI>::kSmemBytes) != cudaSuccess)
       return VIPT_ERR_LAUNCH;
     attr_set = true;
   }
-  const int tiles = ((op.p.M + 255) / 256) * (op.p.N / BN);
+  const int tiles = op.p.tail_from + (((op.p.M + 255) / 256) * (op.p.N / BN) - op.p.tail_from) * op.p.tail_split;
   int grid = 2 * tiles;
   const int cap = num_sms & ~1;
   if (grid > cap) grid = cap;
-  return launch_pdl(gemm2_kernel<EPI, BN>, grid, g2::kThreads, g2::Cfg<BN>::kSmemBytes, st, op.tmA, op.tmB, op.tmC, op.p) == cudaSuccess
+  return launch_pdl(gemm2_kernel<EPI, BN>, grid, g2::kThreads, g2::Cfg<BN, EPI>::kSmemBytes, st, op.tmA, op.tmB, op.tmC, op.tmC2,
+                    op.tmB2, op.p) == cudaSuccess
              ? VIPT_OK
              : VIPT_ERR_LAUNCH;
 }
@@ -323,6 +499,10 @@ int gemm2_launch(const GemmOp& op, int num_sms, cudaStream_t st) {
     case EPI_GELU_F16: return narrow ? launch2_t<EPI_GELU_F16, 128>(op, num_sms, st) : launch2_t<EPI_GELU_F16, 256>(op, num_sms, st);
     case EPI_RELU_F16: return narrow ? launch2_t<EPI_RELU_F16, 128>(op, num_sms, st) : launch2_t<EPI_RELU_F16, 256>(op, num_sms, st);
     case EPI_BIAS_F32: return narrow ? launch2_t<EPI_BIAS_F32, 128>(op, num_sms, st) : launch2_t<EPI_BIAS_F32, 256>(op, num_sms, st);
+    // LayerNorm fold: 256-wide pair tiles only
+    case EPI_RESID_STAT: return narrow ? VIPT_ERR_ARG : launch2_t<EPI_RESID_STAT, 256>(op, num_sms, st);
+    case EPI_LNFOLD_F16: return narrow ? VIPT_ERR_ARG : launch2_t<EPI_LNFOLD_F16, 256>(op, num_sms, st);
+    case EPI_LNFOLD_GELU_F16: return narrow ? VIPT_ERR_ARG : launch2_t<EPI_LNFOLD_GELU_F16, 256>(op, num_sms, st);
   }
   return VIPT_ERR_ARG;
 }
@@ -330,7 +510,8 @@ int gemm2_launch(const GemmOp& op, int num_sms, cudaStream_t st) {
 // same operand conventions as gemm_plan, single group, N % 256 == 0; W box = 128 rows (half tile per CTA)
 int gemm2_plan(GemmOp* op, const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, int epi,
                void* out, int64_t ldc, const float* bias, int num_clusters) {
-  if (K % g2::BK != 0 || N % 128 != 0 || M <= 0 || epi == EPI_RESID_F32) return VIPT_ERR_ARG;
+  if (K % g2::BK != 0 || N % 128 != 0 || M <= 0 || epi == EPI_RESID_F32 || epi == EPI_RESID_STAT) return VIPT_ERR_ARG;
+  if ((epi == EPI_LNFOLD_F16 || epi == EPI_LNFOLD_GELU_F16) && N % 256 != 0) return VIPT_ERR_ARG;
   // 128-wide pair tiles only when N is not a multiple of 256 (or forced, num_clusters < 0).  Choosing them for the
   // N = 768 layers to shorten the last wave (480 half-tiles = 3.5 rounds instead of 4) was measured and lost:
   // linear GEMMs 2.25 -> 2.32 ms per step, the narrow tile moves 1.5x the operand bytes per flop.
@@ -355,13 +536,60 @@ int gemm2_plan(GemmOp* op, const void* A, int64_t lda, const void* W, int64_t ld
   uint32_t bc[3] = {(uint32_t)(epi == EPI_BIAS_F32 ? 32 : g2::kSlabCols), g2::BM, 1};
   r = epi == EPI_BIAS_F32 ? make_tmap_f32(&op->tmC, out, 3, dc, sc, bc) : make_tmap_f16(&op->tmC, out, 3, dc, sc, bc);
   if (r) return r;
+  op->tmC2 = op->tmC;
+  op->tmB2 = op->tmB;
+  // Tail of the persistent loop: T tiles over C clusters leave the last round partly empty (N = 768 at 64 x 320 rows:
+  // 240 tiles = 3.24 rounds of 74, run as 4).  The tiles of that round are cut into 2 or 4 column strips when the strips
+  // still fit ONE round; a strip costs more than its share of a tile (the A operand stream does not shrink: measured
+  // 0.59 of a tile for a half, round 2), so the split must pay for itself.
+  op->p.tail_from = ((M + 255) / 256) * (N / bn);
+  op->p.tail_split = 1;
+  if (num_clusters > 0 && bn == 256 && epi != EPI_BIAS_F32) {      // (fp32 outputs: 32-column slabs, not cut)
+    const int T = op->p.tail_from, rem = T % num_clusters;
+    static const char* off = getenv("VIPT_NO_TAIL_SPLIT");
+    if (!off && T > num_clusters && rem > 0) {
+      int split = rem * 4 <= num_clusters ? 4 : rem * 2 <= num_clusters ? 2 : 1;
+      if (split > 1) {
+        uint32_t bb2[3] = {g2::BK, (uint32_t)(bn / split / 2), 1};
+        r = make_tmap_f16(&op->tmB2, W, 3, db, sb, bb2);
+        if (r) return r;
+        op->p.tail_from = T - rem;
+        op->p.tail_split = split;
+      }
+    }
+  }
   op->p.M = M; op->p.N = N; op->p.K = K; op->p.G = 1;
   op->p.out = out; op->p.ldc = ldc; op->p.out_group_stride = 0; op->p.out_group_col = 0;
   op->p.bias = bias; op->p.resid = nullptr;
   op->p.conv_cb_per_tap = 0; op->p.conv_cin_stride = 0;
+  op->p.stat_out = nullptr; op->p.stat_in = nullptr; op->p.stat_parts = 0; op->p.colsum = nullptr; op->p.ln_eps = 0.f;
   op->bn = bn == 256 ? 512 : 640;      // marks a 2-CTA plan (256- / 128-wide pair tiles)
   op->epi = epi;
   return VIPT_OK;
+}
+
+int gemm2_plan_resid_stat(GemmOp* op, const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, float* x,
+                          void* x16, const float* bias, float2* stat_out) {
+  if (N % 256 != 0 || !x || !x16 || !stat_out) return VIPT_ERR_ARG;
+  // A / W maps and the fp32 map over x (box 32 columns x 128 rows, loaded and stored) come from the fp32-output plan
+  int r = gemm2_plan(op, A, lda, W, ldw, M, N, K, EPI_BIAS_F32, x, N, bias, 0);
+  if (r) return r;
+  if (reinterpret_cast<uintptr_t>(x16) & 15) return VIPT_ERR_ARG;
+  uint64_t dc[3] = {(uint64_t)N, (uint64_t)M, 1};
+  uint64_t sc[2] = {(uint64_t)N * 2, (uint64_t)M * N * 2};
+  uint32_t bc[3] = {32, g2::BM, 1};
+  r = make_tmap_ex(&op->tmC2, 0, 64, x16, 3, dc, sc, bc);
+  if (r) return r;
+  op->p.stat_out = stat_out;
+  op->epi = EPI_RESID_STAT;
+  return VIPT_OK;
+}
+
+void gemm2_set_lnfold(GemmOp* op, const float2* stat_in, int stat_parts, const float* colsum, float ln_eps) {
+  op->p.stat_in = stat_in;
+  op->p.stat_parts = stat_parts;
+  op->p.colsum = colsum;
+  op->p.ln_eps = ln_eps;
 }
 
 int gemm2_plan_conv(GemmOp* op, const void* feat, int c_total, int cin, const void* W, int B, int N, int epi, void* out,

@@ -25,6 +25,7 @@ def _ref(A, W, bias, epi, resid):
     (20480, 768, 3072, 512, 0), (9792, 768, 768, 512, 2), (130, 256, 128, 512, 1),
     (20480, 768, 3072, 640, 0), (15616, 768, 768, 640, 0), (300, 128, 64, 640, 1), (777, 384, 768, 640, 2),   # 128-wide pair tiles
     (1000, 768, 768, 512, 3), (20480, 768, 768, 512, 3), (300, 128, 64, 640, 3),                              # 2-CTA kernel, fp32 out
+    (15616, 768, 768, 512, 0), (5000, 3072, 768, 512, 1), (19000, 768, 3072, 512, 0),      # last round cut into column strips
     (500, 128, 2304, 128, 2), (300, 64, 1152, 64, 2), (260, 32, 576, 32, 2), (20480, 768, 768, 256, 4),
 ])
 def test_gemm(M, N, K, bn, epi):
@@ -46,3 +47,59 @@ def test_gemm(M, N, K, bn, epi):
         print("bad count", bad.shape[0], "first", bad[:8].tolist(), "last", bad[-8:].tolist())
         print("out", out[:2, :8], "ref", ref[:2, :8])
     assert err < tol, (err, tol)
+
+
+@pytest.mark.parametrize("M,N,K", [(256, 256, 64), (300, 768, 768), (20480, 768, 768), (9792, 768, 3072), (130, 512, 128)])
+def test_gemm_resid_stat(M, N, K):
+    """LayerNorm fold, producer (gemm2.cu EPI_RESID_STAT): x += A W^T + b in place (fp32), fp16 copy, per-row partial sums."""
+    L = _lib.lib()
+    g = torch.Generator(device="cuda").manual_seed(M + N + K)
+    A = (torch.randn(M, K, device="cuda", generator=g) * 0.5).half()
+    W = (torch.randn(N, K, device="cuda", generator=g) * 0.05).half()
+    bias = torch.randn(N, device="cuda", generator=g)
+    x0 = torch.randn(M, N, device="cuda", generator=g) * 2 + 0.3
+    x = x0.clone()
+    x16 = torch.full((M, N), float("nan"), device="cuda", dtype=torch.float16)
+    parts = 2 * N // 256
+    stat = torch.full((parts, M, 2), float("nan"), device="cuda")
+    _lib.check(L.vipt_op_gemm_resid_stat(_lib.ptr(A), K, _lib.ptr(W), K, M, N, K, _lib.ptr(x), _lib.ptr(x16), _lib.ptr(bias),
+                                         _lib.ptr(stat), _lib.stream_ptr()), "vipt_op_gemm_resid_stat")
+    torch.cuda.synchronize()
+    ref = x0 + A.float() @ W.float().t() + bias
+    assert (x - ref).abs().max().item() < 1e-3
+    assert torch.equal(x16, x.half())                                # the fp16 copy is the rounding of the stored fp32 value
+    # part 2 * tile + h = the 16-column groups h, h + 2, h + 4, .. of the 256-column tile (one epilogue thread's columns)
+    xp = x.view(M, N // 256, 8, 2, 16).permute(0, 1, 3, 2, 4).reshape(M, parts, 128)
+    assert (stat[..., 0].t() - xp.sum(-1)).abs().max().item() < 2e-3
+    assert ((stat[..., 1].t() - (xp * xp).sum(-1)).abs() / (xp * xp).sum(-1)).max().item() < 1e-5
+
+
+@pytest.mark.parametrize("M,N,gelu", [(256, 256, 0), (300, 2304, 0), (20480, 3072, 1), (9792, 3072, 1), (130, 512, 1),
+                                         (15616, 2304, 0)])        # last round in column strips
+def test_gemm_lnfold(M, N, gelu):
+    """LayerNorm fold, consumer (EPI_LNFOLD_*): with W' = fp16(gamma W0), colsum(W'), bias' = b0 + W0 beta and the row
+    statistics of x, the GEMM over fp16(x) is LayerNorm(x) W0^T + b0 (attn_blocks.py:94,103) to fp16-operand accuracy."""
+    L = _lib.lib()
+    K = 768
+    g = torch.Generator(device="cuda").manual_seed(M + N)
+    x = torch.randn(M, K, device="cuda", generator=g) * (0.5 + 3 * torch.rand(M, 1, device="cuda", generator=g)) + \
+        0.3 * torch.randn(M, 1, device="cuda", generator=g)
+    gamma = 1 + 0.2 * torch.randn(K, device="cuda", generator=g)
+    beta = 0.1 * torch.randn(K, device="cuda", generator=g)
+    W0 = torch.randn(N, K, device="cuda", generator=g) * 0.03
+    b0 = torch.randn(N, device="cuda", generator=g)
+    Wf = (W0 * gamma).half()
+    colsum = Wf.float().sum(1).contiguous()
+    bias = (b0 + W0 @ beta).contiguous()
+    x16 = x.half()
+    xp = x.view(M, 6, 128)
+    stat = torch.stack([xp.sum(-1), (xp * xp).sum(-1)], -1).permute(1, 0, 2).contiguous()      # (6, M, 2)
+    out = torch.full((M, N), float("nan"), device="cuda", dtype=torch.float16)
+    _lib.check(L.vipt_op_gemm_lnfold(_lib.ptr(x16), K, _lib.ptr(Wf), K, M, N, K, gelu, _lib.ptr(out), N, _lib.ptr(bias),
+                                     _lib.ptr(colsum), _lib.ptr(stat), 6, 1e-6, _lib.stream_ptr()), "vipt_op_gemm_lnfold")
+    torch.cuda.synchronize()
+    ref = torch.nn.functional.layer_norm(x.double(), (K,), gamma.double(), beta.double(), 1e-6) @ W0.double().t() + b0.double()
+    if gelu:
+        ref = torch.nn.functional.gelu(ref)
+    err = (out.double() - ref).abs().max().item()
+    assert err < 4e-3 * max(1.0, ref.abs().max().item()), err
