@@ -33,8 +33,9 @@ int vipt_op_gemm(const void* A, int64_t lda, const void* W, int64_t ldw, int M, 
 
 /* LayerNorm folded into a GEMM pair (north star (b); ViPT/lib/models/layers/attn_blocks.py:94,103: x = x + proj(..);
  * mlp(norm2(x))), 2-CTA kernel, N % 256 == 0.
- * Producer: x (M,N) fp32 <- x + A W^T + bias in place, x16 (M,N) fp16 = the updated rows, stat_out (2*N/256, M, 2)
- * fp32 = per-row (sum, sum of squares) of 128 columns each (part 2t + h: the 16-column groups h, h+2, .. of tile t). */
+ * Producer: x (M,N) fp32 <- x + A W^T + bias in place, x16 (M,N) fp16 = the updated rows, stat_out (N/32, M, 2)
+ * fp32 = per-row (sum, sum of squares) of 32 columns each (part 2g + h: the 16-column groups h and h+2 of columns
+ * [64g, 64g+64)). */
 int vipt_op_gemm_resid_stat(const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, float* x, void* x16,
                             const float* bias, float* stat_out, void* stream);
 /* Consumer: out fp16 = [gelu](rstd * (A W^T - mean * colsum) + bias) with mean / rstd of every row of A (width K) from

@@ -37,7 +37,7 @@ int vipt_op_gemm(const void* A, int64_t lda, const void* W, int64_t ldw, int M, 
 int vipt_op_gemm_resid_stat(const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, float* x, void* x16,
                             const float* bias, float* stat_out, void* stream) {
   vipt::GemmOp op;
-  int r = vipt::gemm2_plan_resid_stat(&op, A, lda, W, ldw, M, N, K, x, x16, bias, (float2*)stat_out);
+  int r = vipt::gemm2_plan_resid_stat(&op, A, lda, W, ldw, M, N, K, x, x16, bias, (float2*)stat_out, num_sms() / 2);
   if (r) { set_err("gemm2_plan_resid_stat failed"); return r; }
   r = vipt::gemm_launch(op, num_sms(), (cudaStream_t)stream);
   if (r) set_err(cudaGetErrorString(cudaGetLastError()));

@@ -63,7 +63,7 @@ struct Engine {
   // activations
   __half *apatch, *xn, *dbuf, *qkv, *att, *hbuf, *feat16, *h1, *h2, *h3, *h4;
   float *E, *xA, *xB, *XD, *FV, *ce_prob, *ce_score, *feat32;
-  float2* lnstat = nullptr;           // LayerNorm fold: (6, B * 320) partial (sum, sum of squares) per row
+  float2* lnstat = nullptr;           // LayerNorm fold: (24, B * 320) partial (sum, sum of squares) per row
   int *giA, *giB, *perm, *removed, *slot_of_pos, *ident, *err;
   // outputs / state
   float *score_map, *size_map, *offset_map, *pred_boxes, *out_scores;

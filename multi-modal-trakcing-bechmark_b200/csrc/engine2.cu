@@ -46,7 +46,7 @@ int Engine::finalize_buffers() {
   AL(apatch, __half, 2 * R * 768);
   AL(E, float, 2 * R * 768);
   AL(xA, float, R * 768); AL(xB, float, R * 768);
-  AL(XD, float, R * 16); AL(FV, float, R * 8); AL(lnstat, float2, 6 * R);
+  AL(XD, float, R * 16); AL(FV, float, R * 8); AL(lnstat, float2, 24 * R);
   AL(xn, __half, R * 768); AL(dbuf, __half, R * 768); AL(qkv, __half, R * 2304); AL(att, __half, R * 768); AL(hbuf, __half, R * 3072);
   AL(ce_prob, float, (size_t)B * kHeads * kLensX); AL(ce_score, float, 3 * RH);
   AL(feat16, __half, RH * 768); AL(feat32, float, R * 768);
@@ -110,7 +110,7 @@ int Engine::finalize_buffers() {
     // the consumer GEMM applies mean / rstd in its epilogue
     if (L[i].fuse_ln1) {
       RET(gemm2_plan(&g_qkv[i], xn, 768, L[i].w_qkv, 768, Ma, 2304, 768, EPI_LNFOLD_F16, qkv, 2304, L[i].b_qkv, num_sms / 2));
-      gemm2_set_lnfold(&g_qkv[i], lnstat, 6, L[i].cs_qkv, 1e-6f);
+      gemm2_set_lnfold(&g_qkv[i], lnstat, 24, L[i].cs_qkv, 1e-6f);
     } else {
       RET(plan_lin(&g_qkv[i], xn, 768, L[i].w_qkv, Ma, 2304, 768, EPI_BIAS_F16, qkv, L[i].b_qkv));
     }
@@ -118,16 +118,16 @@ int Engine::finalize_buffers() {
     // otherwise proj / fc2 write their branch output as fp16 (dbuf); the residual add is fused into the next
     // LayerNorm / prompt kernel, where it is coalesced
     if (L[i].fuse_ln2) {
-      RET(gemm2_plan_resid_stat(&g_proj[i], att, 768, L[i].w_proj, 768, Ma, 768, 768, x_cur, xn, L[i].b_proj, lnstat));
+      RET(gemm2_plan_resid_stat(&g_proj[i], att, 768, L[i].w_proj, 768, Ma, 768, 768, x_cur, xn, L[i].b_proj, lnstat, num_sms / 2));
       RET(gemm2_plan(&g_fc1[i], xn, 768, L[i].w_fc1, 768, Mm, 3072, 768, EPI_LNFOLD_GELU_F16, hbuf, 3072, L[i].b_fc1, num_sms / 2));
-      gemm2_set_lnfold(&g_fc1[i], lnstat, 6, L[i].cs_fc1, 1e-6f);
+      gemm2_set_lnfold(&g_fc1[i], lnstat, 24, L[i].cs_fc1, 1e-6f);
     } else {
       RET(plan_lin(&g_proj[i], att, 768, L[i].w_proj, Ma, 768, 768, EPI_BIAS_F16, dbuf, L[i].b_proj));
       RET(plan_lin(&g_fc1[i], xn, 768, L[i].w_fc1, Mm, 3072, 768, EPI_GELU_F16, hbuf, L[i].b_fc1));
     }
     if (ce_keep[i]) { float* t = x_cur; x_cur = x_oth; x_oth = t; }
     if (i + 1 < kDepth && L[i + 1].fuse_ln1) {
-      RET(gemm2_plan_resid_stat(&g_fc2[i], hbuf, 3072, L[i].w_fc2, 3072, Mm, 768, 3072, x_cur, xn, L[i].b_fc2, lnstat));
+      RET(gemm2_plan_resid_stat(&g_fc2[i], hbuf, 3072, L[i].w_fc2, 3072, Mm, 768, 3072, x_cur, xn, L[i].b_fc2, lnstat, num_sms / 2));
     } else {
       RET(plan_lin(&g_fc2[i], hbuf, 3072, L[i].w_fc2, Mm, 768, 3072, EPI_BIAS_F16, dbuf, L[i].b_fc2));
     }

@@ -16,7 +16,7 @@ enum GemmEpilogue {
   EPI_RESID_F32 = 4,   // out fp32 = resid + acc + bias              (attn.proj, mlp.fc2; in place allowed)
   // LayerNorm fused into the GEMMs (2-CTA kernel only; gemm2.cu "LayerNorm fold"):
   EPI_RESID_STAT = 5,       // producer: x (fp32, in place) += acc + bias; x16 = fp16(x); per-row partial (sum, sum of
-                            // squares) of every 128-column half tile            (attn.proj, mlp.fc2)
+                            // squares) over 32 columns each                     (attn.proj, mlp.fc2)
   EPI_LNFOLD_F16 = 6,       // consumer: out fp16 = rstd * (acc - mean * colsum) + bias, W pre-scaled by the LayerNorm
                             // gain, bias = b + W beta                           (attn.qkv after norm1)
   EPI_LNFOLD_GELU_F16 = 7,  // consumer: the same followed by GELU              (mlp.fc1 after norm2)
@@ -36,7 +36,7 @@ struct GemmParams {
   int conv_cb_per_tap;
   int conv_cin_stride;
   // LayerNorm fold: statistics travel as (parts, M) float2 = (sum, sum of squares) over a part's columns
-  float2* stat_out;          // EPI_RESID_STAT: parts = 2 * N / 256, part = 2 * tile_n + h (16-column groups h, h + 2, ..)
+  float2* stat_out;          // EPI_RESID_STAT: parts = N / 32, part 2 g + h = the 16-column groups h and h + 2 of the 64 columns g
   const float2* stat_in;     // EPI_LNFOLD_*: partial sums of the K-wide rows of A
   int stat_parts;
   const float* colsum;       // EPI_LNFOLD_*: (N) sum over k of the fp16 weight row
@@ -70,9 +70,9 @@ int gemm_launch(const GemmOp& op, int num_sms, cudaStream_t st);   // dispatches
 int gemm2_plan(GemmOp* op, const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, int epi,
                void* out, int64_t ldc, const float* bias, int num_clusters = 0);
 int gemm2_launch(const GemmOp& op, int num_sms, cudaStream_t st);
-// LayerNorm fold, producer: x (M, N) fp32 ld N updated in place, x16 (M, N) fp16, stat_out (2 * N / 256, M)
+// LayerNorm fold, producer: x (M, N) fp32 ld N updated in place, x16 (M, N) fp16, stat_out (N / 32, M)
 int gemm2_plan_resid_stat(GemmOp* op, const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, float* x,
-                          void* x16, const float* bias, float2* stat_out);
+                          void* x16, const float* bias, float2* stat_out, int num_clusters = 0);
 // LayerNorm fold, consumer: gemm2_plan(.., epi = EPI_LNFOLD_*, ..) followed by this
 void gemm2_set_lnfold(GemmOp* op, const float2* stat_in, int stat_parts, const float* colsum, float ln_eps);
 int make_tmap_ex(CUtensorMap* out, int dtype_f32, int swizzle_bytes, const void* base, int rank, const uint64_t* dims,

@@ -45,13 +45,14 @@ constexpr int kResidRing = 3;      // EPI_RESID_STAT: fp32 slabs of x in flight 
 template <int BN, int EPI>
 struct Cfg {
   static constexpr bool kResid = EPI == EPI_RESID_STAT;
-  static constexpr int kStages = kResid ? 4 : (BN == 256 ? 5 : 6);
+  static constexpr int kStages = kResid ? 3 : (BN == 256 ? 5 : 6);
   static constexpr int kBBytes = (BN / 2) * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   // 4 staging slabs: 2 for fp16 outputs (double-buffered 64-column slabs; the LayerNorm-fold consumers keep the column
   // sums in the third), 4 for fp32 outputs (two 32-column slabs per step).  EPI_RESID_STAT: 3 fp32 slabs in (128 rows x
-  // 32 columns), 2 fp32 slabs out, 2 half-size fp16 slabs out.
-  static constexpr int kSlabs = kResid ? kResidRing + 3 : 4;
+  // 32 columns), 3 fp32 slabs out, 3 half-size fp16 slabs out (a store may still be reading its slab while the next
+  // step is staged: with two slabs every step waited for the previous store to drain, the largest stall of the kernel).
+  static constexpr int kSlabs = kResid ? kResidRing + 5 : 4;
   static constexpr int kSmemBytes =
       1024 + kStages * kStageBytes + kSlabs * kSlabBytes + BN * 4 + (2 * kStages + 4 + 2 * kResidRing) * 8 + 16;
 };
@@ -134,6 +135,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   uint8_t* slab = smem + kStages * kStageBytes;            // 2 x 16 KB output staging (TMA store source)
   float* bias_s = reinterpret_cast<float*>(slab + Cfg<BN, EPI>::kSlabs * kSlabBytes);
   float* cs_s = reinterpret_cast<float*>(slab + 2 * kSlabBytes);      // kFold: column sums (fp16 outputs use 2 slabs)
+  float2* rowstat_s = reinterpret_cast<float2*>(slab + 2 * kSlabBytes + 4096);   // kFold: [2][128] (rstd, -mean * rstd)
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(bias_s + BN);
   uint64_t* empty_bar = full_bar + kStages;
   uint64_t* tfull_bar = empty_bar + kStages;
@@ -260,15 +262,55 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
       __syncwarp();
       if (++as == 2) { as = 0; aph ^= 1; }
     }
+  } else if (kFold && warp == 3) {
+    // ------------------------------------------------ row statistics (both CTAs), one tile ahead of the epilogue: the
+    // partial sums of this CTA's 128 rows -> (rstd, -mean * rstd) in shared memory.  (Read by the epilogue threads
+    // themselves, the global-load latency sat on every tile's critical path: fc1 69.6 -> 94.2 us.)
+    const float inv_k = 1.f / (float)p.K;
+    int it = 0;
+    for (int t = cluster_id; t < num_tiles; t += num_clusters, ++it) {
+      const int row0 = unit_of(t).tm * 2 * BM + (int)rank * BM;
+      const int slot = it & 1;
+      mbar_wait(&rempty_bar[slot], ((it >> 1) & 1) ^ 1);
+      // 4 rows per lane; the partial sums of a row are added in part order (the result does not depend on the
+      // schedule), the loads go out in batches of 8 parts x 4 rows so that their latencies overlap
+      float s1[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f};
+      for (int q0 = 0; q0 < p.stat_parts; q0 += 8) {
+        float2 st[4][8];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const int rr = row0 + i * 32 + lane;
+            st[i][u] = (q0 + u < p.stat_parts && rr < p.M) ? __ldg(p.stat_in + (size_t)(q0 + u) * p.M + rr) : make_float2(0.f, 0.f);
+          }
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            s1[i] += st[i][u].x;
+            s2[i] += st[i][u].y;
+          }
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float mean = s1[i] * inv_k;
+        const float rs = rsqrtf(fmaxf(fmaf(-mean, mean, s2[i] * inv_k), 0.f) + p.ln_eps);
+        rowstat_s[slot * BM + i * 32 + lane] = make_float2(rs, -mean * rs);       // (rows >= M: never stored)
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&rfull_bar[slot]);
+    }
   } else if (kResid && warp == 3) {
     // ------------------------------------------------ x slab producer (both CTAs): the fp32 rows this CTA's tile updates,
     // 32 columns at a time, in the order the epilogue consumes them; runs ahead of the epilogue by the ring depth
     int rs = 0;
     uint32_t rph = 0;
     for (int t = cluster_id; t < num_tiles; t += num_clusters) {
-      const int n0 = (t % tiles_n) * BN;          // (no column strips with this epilogue: gemm2_plan_resid_stat)
-      const int row0 = (t / tiles_n) * 2 * BM + (int)rank * BM;
-      for (int j = 0; j < BN / 32; ++j) {
+      const Unit un = unit_of(t);
+      const int n0 = un.n0;
+      const int row0 = un.tm * 2 * BM + (int)rank * BM;
+      for (int j = 0; j < un.width / 32; ++j) {
         mbar_wait(&rempty_bar[rs], rph ^ 1);
         if (elect_one()) {
           mbar_expect_tx(&rfull_bar[rs], kSlabBytes);
@@ -288,31 +330,46 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     uint32_t aph = 0;
     int rs = 0;                  // kResid: x slab ring position
     uint32_t rph = 0;
-    for (int t = cluster_id; t < num_tiles; t += num_clusters) {
+    int it = 0;                  // kFold: tile counter (row statistics slots)
+    int ob = 0;                  // kResid: output slab (0..2), runs on across tiles
+    float next_bias = 0.f, next_cs = 0.f;      // bias / column sum of column `et` of the next tile
+    if (cluster_id < num_tiles) {
+      const Unit nx = unit_of(cluster_id);
+      if (et < nx.width) {
+        next_bias = p.bias ? __ldg(p.bias + nx.n0 + et) : 0.f;
+        if (kFold) next_cs = __ldg(p.colsum + nx.n0 + et);
+      }
+    }
+    for (int t = cluster_id; t < num_tiles; t += num_clusters, ++it) {
       const Unit un = unit_of(t);
       const int tm = un.tm;
       const int n0 = un.n0;
-      const int tn = n0 / BN;
       const int n_slabs = un.width / kSlabCols;
       const int row0 = tm * 2 * BM + (int)rank * BM;           // first row of this CTA's 128 x 256 tile
       const int r = we * 32 + lane;                            // row within the tile == TMEM lane
-      // (bias_s of the previous tile was last read before that tile's final slab barrier)
-      for (int i = et; i < un.width; i += kEpiThreads) bias_s[i] = p.bias ? p.bias[n0 + i] : 0.f;
+      // (bias_s of the previous tile was last read before that tile's final slab barrier.)  The values were fetched
+      // while the previous tile was in the epilogue: read here, the global-load latency sat on every tile's critical
+      // path (ncu: the staging stores were the top stall of the fc1 epilogue after the barrier waits).
+      if (et < un.width) {
+        bias_s[et] = next_bias;
+        if (kFold) cs_s[et] = next_cs;
+      }
+      if (t + num_clusters < num_tiles) {
+        const Unit nx = unit_of(t + num_clusters);
+        if (et < nx.width) {
+          next_bias = p.bias ? __ldg(p.bias + nx.n0 + et) : 0.f;
+          if (kFold) next_cs = __ldg(p.colsum + nx.n0 + et);
+        }
+      }
       float ln_rs = 0.f, ln_nm = 0.f;                          // kFold: rstd and -mean * rstd of this thread's row
       if (kFold) {
-        for (int i = et; i < un.width; i += kEpiThreads) cs_s[i] = p.colsum[n0 + i];
-        if (row0 + r < p.M) {
-          float s1 = 0.f, s2 = 0.f;
-          for (int q = 0; q < p.stat_parts; ++q) {             // fixed order: results do not depend on the schedule
-            const float2 st = p.stat_in[(size_t)q * p.M + row0 + r];
-            s1 += st.x;
-            s2 += st.y;
-          }
-          const float inv_k = 1.f / (float)p.K;
-          const float mean = s1 * inv_k;
-          ln_rs = rsqrtf(fmaxf(fmaf(-mean, mean, s2 * inv_k), 0.f) + p.ln_eps);
-          ln_nm = -mean * ln_rs;
-        }
+        const int slot = it & 1;
+        mbar_wait(&rfull_bar[slot], (it >> 1) & 1);
+        const float2 st = rowstat_s[slot * BM + r];
+        ln_rs = st.x;
+        ln_nm = st.y;
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&rempty_bar[slot]);
       }
       asm volatile("bar.sync 1, 256;" ::: "memory");
       mbar_wait(&tfull_bar[as], aph);
@@ -323,8 +380,9 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         float s1 = 0.f, s2 = 0.f;
         uint32_t v[16];
         tmem_ld16(taddr0, v);
+        const int n_steps = un.width / 32;
 #pragma unroll 1
-        for (int j = 0; j < BN / 32; ++j) {
+        for (int j = 0; j < n_steps; ++j) {
           mbar_wait(&rfull_bar[rs], rph);
           const uint32_t in_row = smem_u32(slab + rs * kSlabBytes) + r * 128;
           const uint32_t brow = bias_u32 + (j * 32 + hh * 16) * 4;
@@ -339,19 +397,24 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
             f[q * 4 + 2] = (__uint_as_float(v[q * 4 + 2]) + bq.z) + xq.z;
             f[q * 4 + 3] = (__uint_as_float(v[q * 4 + 3]) + bq.w) + xq.w;
           }
-          if (j + 1 < BN / 32) tmem_ld16(taddr0 + (j + 1) * 32, v);
+          if (j + 1 < n_steps) tmem_ld16(taddr0 + (j + 1) * 32, v);
 #pragma unroll
           for (int k = 0; k < 16; ++k) {
             s1 += f[k];
             s2 = fmaf(f[k], f[k], s2);
           }
-          const uint32_t o32 = smem_u32(slab + (kResidRing + (j & 1)) * kSlabBytes) + r * 128;
+          if (j & 1) {           // a 64-column group is complete: part 2 * group + hh (this thread's 32 of its columns)
+            if (row0 + r < p.M) p.stat_out[(size_t)(((n0 >> 6) + (j >> 1)) * 2 + hh) * p.M + row0 + r] = make_float2(s1, s2);
+            s1 = 0.f;
+            s2 = 0.f;
+          }
+          const uint32_t o32 = smem_u32(slab + (kResidRing + ob) * kSlabBytes) + r * 128;
 #pragma unroll
           for (int q = 0; q < 4; ++q)
             sts128(o32 + (((hh * 4 + q) ^ (r & 7)) * 16), __float_as_uint(f[q * 4 + 0]), __float_as_uint(f[q * 4 + 1]),
                    __float_as_uint(f[q * 4 + 2]), __float_as_uint(f[q * 4 + 3]));
           // fp16 copy: 128 rows x 32 columns = 64-byte rows, 64-byte swizzle (16-byte chunk ^= (row / 2) % 4)
-          const uint32_t o16 = smem_u32(slab + (kResidRing + 2) * kSlabBytes) + (j & 1) * (kSlabBytes / 2) + r * 64;
+          const uint32_t o16 = smem_u32(slab + (kResidRing + 3) * kSlabBytes) + ob * (kSlabBytes / 2) + r * 64;
 #pragma unroll
           for (int q = 0; q < 2; ++q)
             sts128(o16 + (((hh * 2 + q) ^ ((r >> 1) & 3)) * 16), pack_op2(f[q * 8 + 0], f[q * 8 + 1]),
@@ -360,22 +423,23 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
           __syncwarp();
           if (lane == 0) mbar_arrive(&rempty_bar[rs]);         // the x slab is consumed
           if (++rs == kResidRing) { rs = 0; rph ^= 1; }
-          if (et == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+          // the slab the NEXT step writes was read by the store issued two steps ago: at most one store may be pending
+          if (et == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
           asm volatile("bar.sync 1, 256;" ::: "memory");
           if (et == 0) {
             asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
-                         ::"l"(reinterpret_cast<uint64_t>(&tmC)), "r"(smem_u32(slab + (kResidRing + (j & 1)) * kSlabBytes)),
+                         ::"l"(reinterpret_cast<uint64_t>(&tmC)), "r"(smem_u32(slab + (kResidRing + ob) * kSlabBytes)),
                            "r"(n0 + j * 32), "r"(row0), "r"(0)
                          : "memory");
             asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
                          ::"l"(reinterpret_cast<uint64_t>(&tmC2)),
-                           "r"(smem_u32(slab + (kResidRing + 2) * kSlabBytes) + (j & 1) * (kSlabBytes / 2)), "r"(n0 + j * 32),
+                           "r"(smem_u32(slab + (kResidRing + 3) * kSlabBytes) + ob * (kSlabBytes / 2)), "r"(n0 + j * 32),
                            "r"(row0), "r"(0)
                          : "memory");
             asm volatile("cp.async.bulk.commit_group;" ::: "memory");
           }
+          if (++ob == 3) ob = 0;
         }
-        if (row0 + r < p.M) p.stat_out[(size_t)(tn * 2 + hh) * p.M + row0 + r] = make_float2(s1, s2);
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive_cluster(mapa_cta(smem_u32(&tempty_bar[as]), 0));
@@ -544,7 +608,7 @@ int gemm2_plan(GemmOp* op, const void* A, int64_t lda, const void* W, int64_t ld
   // 0.59 of a tile for a half, round 2), so the split must pay for itself.
   op->p.tail_from = ((M + 255) / 256) * (N / bn);
   op->p.tail_split = 1;
-  if (num_clusters > 0 && bn == 256 && epi != EPI_BIAS_F32) {      // (fp32 outputs: 32-column slabs, not cut)
+  if (num_clusters > 0 && bn == 256) {
     const int T = op->p.tail_from, rem = T % num_clusters;
     static const char* off = getenv("VIPT_NO_TAIL_SPLIT");
     if (!off && T > num_clusters && rem > 0) {
@@ -569,10 +633,10 @@ int gemm2_plan(GemmOp* op, const void* A, int64_t lda, const void* W, int64_t ld
 }
 
 int gemm2_plan_resid_stat(GemmOp* op, const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, float* x,
-                          void* x16, const float* bias, float2* stat_out) {
+                          void* x16, const float* bias, float2* stat_out, int num_clusters) {
   if (N % 256 != 0 || !x || !x16 || !stat_out) return VIPT_ERR_ARG;
   // A / W maps and the fp32 map over x (box 32 columns x 128 rows, loaded and stored) come from the fp32-output plan
-  int r = gemm2_plan(op, A, lda, W, ldw, M, N, K, EPI_BIAS_F32, x, N, bias, 0);
+  int r = gemm2_plan(op, A, lda, W, ldw, M, N, K, EPI_BIAS_F32, x, N, bias, num_clusters);
   if (r) return r;
   if (reinterpret_cast<uintptr_t>(x16) & 15) return VIPT_ERR_ARG;
   uint64_t dc[3] = {(uint64_t)N, (uint64_t)M, 1};

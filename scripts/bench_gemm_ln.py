@@ -35,7 +35,7 @@ for n in (320, 244, 190, 153):
     x = torch.randn(M, 768, device="cuda"); x16 = torch.empty(M, 768, device="cuda", dtype=torch.float16)
     d16 = torch.empty(M, 768, device="cuda", dtype=torch.float16)
     h = torch.empty(M, 3072, device="cuda", dtype=torch.float16)
-    stat = torch.rand(6, M, 2, device="cuda") * 768
+    stat = torch.rand(24, M, 2, device="cuda") * 768
     sp = _lib.stream_ptr()
     res = {}
     if only in ("", "plain"):
@@ -45,5 +45,5 @@ for n in (320, 244, 190, 153):
     if only in ("", "resid"):
         res["proj_resid_stat"] = timeit(lambda: _lib.check(L.vipt_op_gemm_resid_stat(_lib.ptr(att), 768, _lib.ptr(Wp), 768, M, 768, 768, _lib.ptr(x), _lib.ptr(x16), _lib.ptr(bp), _lib.ptr(stat), sp)))
     if only in ("", "fold"):
-        res["fc1_lnfold"] = timeit(lambda: _lib.check(L.vipt_op_gemm_lnfold(_lib.ptr(x16), 768, _lib.ptr(W1), 768, M, 3072, 768, 1, _lib.ptr(h), 3072, _lib.ptr(b1), _lib.ptr(cs), _lib.ptr(stat), 6, 1e-6, sp)))
+        res["fc1_lnfold"] = timeit(lambda: _lib.check(L.vipt_op_gemm_lnfold(_lib.ptr(x16), 768, _lib.ptr(W1), 768, M, 3072, 768, 1, _lib.ptr(h), 3072, _lib.ptr(b1), _lib.ptr(cs), _lib.ptr(stat), 24, 1e-6, sp)))
     print("B=%d n=%d M=%d  " % (B, n, M) + "  ".join("%s %.1f us" % kv for kv in res.items()), flush=True)

@@ -49,7 +49,8 @@ def test_gemm(M, N, K, bn, epi):
     assert err < tol, (err, tol)
 
 
-@pytest.mark.parametrize("M,N,K", [(256, 256, 64), (300, 768, 768), (20480, 768, 768), (9792, 768, 3072), (130, 512, 128)])
+@pytest.mark.parametrize("M,N,K", [(256, 256, 64), (300, 768, 768), (20480, 768, 768), (9792, 768, 3072), (130, 512, 128),
+                                   (15616, 768, 768), (19000, 768, 3072)])      # the last two: tail in column strips
 def test_gemm_resid_stat(M, N, K):
     """LayerNorm fold, producer (gemm2.cu EPI_RESID_STAT): x += A W^T + b in place (fp32), fp16 copy, per-row partial sums."""
     L = _lib.lib()
@@ -60,7 +61,7 @@ def test_gemm_resid_stat(M, N, K):
     x0 = torch.randn(M, N, device="cuda", generator=g) * 2 + 0.3
     x = x0.clone()
     x16 = torch.full((M, N), float("nan"), device="cuda", dtype=torch.float16)
-    parts = 2 * N // 256
+    parts = N // 32
     stat = torch.full((parts, M, 2), float("nan"), device="cuda")
     _lib.check(L.vipt_op_gemm_resid_stat(_lib.ptr(A), K, _lib.ptr(W), K, M, N, K, _lib.ptr(x), _lib.ptr(x16), _lib.ptr(bias),
                                          _lib.ptr(stat), _lib.stream_ptr()), "vipt_op_gemm_resid_stat")
@@ -68,8 +69,8 @@ def test_gemm_resid_stat(M, N, K):
     ref = x0 + A.float() @ W.float().t() + bias
     assert (x - ref).abs().max().item() < 1e-3
     assert torch.equal(x16, x.half())                                # the fp16 copy is the rounding of the stored fp32 value
-    # part 2 * tile + h = the 16-column groups h, h + 2, h + 4, .. of the 256-column tile (one epilogue thread's columns)
-    xp = x.view(M, N // 256, 8, 2, 16).permute(0, 1, 3, 2, 4).reshape(M, parts, 128)
+    # part 2 g + h = the 16-column groups h and h + 2 of columns [64 g, 64 g + 64) (one epilogue thread's columns)
+    xp = x.view(M, N // 64, 2, 2, 16).permute(0, 1, 3, 2, 4).reshape(M, parts, 32)
     assert (stat[..., 0].t() - xp.sum(-1)).abs().max().item() < 2e-3
     assert ((stat[..., 1].t() - (xp * xp).sum(-1)).abs() / (xp * xp).sum(-1)).max().item() < 1e-5
 
@@ -92,11 +93,11 @@ def test_gemm_lnfold(M, N, gelu):
     colsum = Wf.float().sum(1).contiguous()
     bias = (b0 + W0 @ beta).contiguous()
     x16 = x.half()
-    xp = x.view(M, 6, 128)
-    stat = torch.stack([xp.sum(-1), (xp * xp).sum(-1)], -1).permute(1, 0, 2).contiguous()      # (6, M, 2)
+    xp = x.view(M, 24, 32)
+    stat = torch.stack([xp.sum(-1), (xp * xp).sum(-1)], -1).permute(1, 0, 2).contiguous()      # (24, M, 2)
     out = torch.full((M, N), float("nan"), device="cuda", dtype=torch.float16)
     _lib.check(L.vipt_op_gemm_lnfold(_lib.ptr(x16), K, _lib.ptr(Wf), K, M, N, K, gelu, _lib.ptr(out), N, _lib.ptr(bias),
-                                     _lib.ptr(colsum), _lib.ptr(stat), 6, 1e-6, _lib.stream_ptr()), "vipt_op_gemm_lnfold")
+                                     _lib.ptr(colsum), _lib.ptr(stat), 24, 1e-6, _lib.stream_ptr()), "vipt_op_gemm_lnfold")
     torch.cuda.synchronize()
     ref = torch.nn.functional.layer_norm(x.double(), (K,), gamma.double(), beta.double(), 1e-6) @ W0.double().t() + b0.double()
     if gelu:
