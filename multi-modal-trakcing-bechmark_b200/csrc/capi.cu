@@ -119,6 +119,7 @@ int vipt_engine_create(void** out) {
   e->opt_zero_copy = getenv("VIPT_NO_ZEROCOPY") == nullptr;
   e->opt_speculate = getenv("VIPT_NO_SPECULATION") == nullptr;
   e->opt_lnfold = getenv("VIPT_NO_LNFOLD") == nullptr;
+  e->opt_promptfold = getenv("VIPT_NO_PROMPT_FOLD") == nullptr;
   *out = e;
   return VIPT_OK;
 }
@@ -214,6 +215,7 @@ int64_t vipt_engine_info(void* ev, const char* what) {
   if (!e || !what) return -1;
   if (!strcmp(what, "launches_per_step")) return e->launches_per_step;
   if (!strcmp(what, "batch")) return e->B;
+  if (!strcmp(what, "promptfold_layers")) { int n = 0; for (int i = 0; i < vipt::kDepth; ++i) n += e->PW[i].fold_on; return n; }
   if (!strcmp(what, "lnfold_layers")) { int n = 0; for (int i = 0; i < vipt::kDepth; ++i) n += e->L[i].fuse_ln2 + e->L[i].fuse_ln1; return n; }
   if (!strcmp(what, "final_tokens")) return e->n_tok[vipt::kDepth];
   if (!strncmp(what, "n_tok_", 6)) { int i = atoi(what + 6); return (i >= 0 && i <= vipt::kDepth) ? e->n_tok[i] : -1; }

@@ -133,6 +133,9 @@ void Engine::plan_schedule() {
     auto pair = [&](int n) { return ((B * n + 255) / 256) * 3 >= num_sms / 2; };
     L[i].fuse_ln2 = opt_lnfold && !ce_keep[i] && pair(n_tok[i]);
     L[i].fuse_ln1 = opt_lnfold && !deep && i >= 1 && pair(n_tok[i]);
+    // prompt fold: the deep-prompt stage of layer i inside the epilogues of fc2[i-1], qkv[i] and proj[i]; proj must be
+    // the residual kind, so not in the candidate-elimination layers (they keep prompt_coop_kernel)
+    PW[i].fold_on = opt_promptfold && deep && i >= 1 && L[i].fuse_ln2;
   }
 }
 
@@ -290,6 +293,60 @@ int Engine::finalize(int batch, bool deep_prompt) {
       fold[160] = (float)(c0 / 768.0);
       fold[161] = PW[i].smooth;
       PW[i].fold = pk.up_f32(fold.data(), fold.size());
+      if (PW[i].fold_on) {
+        // u = this block's conv1x1 (768, 8) and bias b1: x = v + U f + b1
+        std::vector<float> c20((size_t)768 * 20, 0.f), f2(112, 0.f);
+        double su[8] = {0}, sb = 0, G9[81] = {0};
+        for (int c = 0; c < 768; ++c) {
+          double ue[9];
+          for (int k = 0; k < 8; ++k) {
+            c20[(size_t)c * 20 + k] = wga[k * 768 + c];
+            c20[(size_t)c * 20 + 8 + k] = w1[c * 8 + k];
+            ue[k] = w1[c * 8 + k];
+            su[k] += ue[k];
+          }
+          const float b1c = (*pk.get(p + "conv1x1.bias", 768))[c];
+          c20[(size_t)c * 20 + 16] = b1c;
+          ue[8] = b1c;
+          sb += b1c;
+          for (int a = 0; a < 9; ++a)
+            for (int q = 0; q < 9; ++q) G9[a * 9 + q] += ue[a] * ue[q];
+        }
+        for (int k = 0; k < 8; ++k) { f2[k] = sc[k]; f2[8 + k] = (float)su[k]; }
+        f2[16] = (float)sb;
+        for (int q = 0; q < 81; ++q) f2[24 + q] = (float)G9[q];
+        PW[i].colw20 = pk.up_f32(c20.data(), c20.size());
+        PW[i].fold2 = pk.up_f32(f2.data(), f2.size());
+        // attn.qkv of this block over x16 = fp16(v): W' = fp16(gamma1 * Wqkv); the rank-8 update enters as W'U, W'b1
+        const std::string bp = bb + "blocks." + std::to_string(i) + ".";
+        const auto& b1v = *pk.get(p + "conv1x1.bias", 768);
+        std::vector<float> wf, bf, cs;
+        fold_ln(*pk.get(bp + "attn.qkv.weight", 2304 * 768), *pk.get(bp + "attn.qkv.bias", 2304), *pk.get(bp + "norm1.weight", 768),
+                *pk.get(bp + "norm1.bias", 768), 2304, wf, bf, cs);
+        L[i].w_qkv = pk.up_f16(wf.data(), wf.size());
+        std::vector<float> wxq((size_t)2304 * 64, 0.f), wxp((size_t)768 * 64, 0.f), bq(2304);
+        for (int n = 0; n < 2304; ++n) {
+          double wu[8] = {0}, wb = 0;
+          for (int c = 0; c < 768; ++c) {
+            const double wv = (double)__half2float(__float2half_rn(wf[(size_t)n * 768 + c]));
+            for (int k = 0; k < 8; ++k) wu[k] += wv * (double)w1[c * 8 + k];
+            wb += wv * (double)b1v[c];
+          }
+          for (int k = 0; k < 8; ++k) wxq[(size_t)n * 64 + k] = (float)wu[k];
+          wxq[(size_t)n * 64 + 8] = (float)wb;      // W'b1 is scaled by rstd like the rest of x W'^T: column 8 of Ax is 1
+          bq[n] = bf[n];
+        }
+        for (int c = 0; c < 768; ++c)
+          for (int k = 0; k < 8; ++k) wxp[(size_t)c * 64 + k] = w1[c * 8 + k];
+        PW[i].wx_qkv = pk.up_f16(wxq.data(), wxq.size());
+        PW[i].wx_proj = pk.up_f16(wxp.data(), wxp.size());
+        PW[i].b_qkv_r8 = pk.up_f32(bq.data(), bq.size());
+        PW[i].cs_qkv_r8 = pk.up_f32(cs.data(), cs.size());
+        const auto& bpj = *pk.get(bp + "attn.proj.bias", 768);
+        std::vector<float> br(768);
+        for (int c = 0; c < 768; ++c) br[c] = bpj[c] + b1v[c];
+        PW[i].b_proj_r8 = pk.up_f32(br.data(), 768);
+      }
     }
   }
   // ---- center head: towers ctr | offset | size; BN folded

@@ -34,6 +34,11 @@ struct PromptW {
   float *wg_a, *wg_d, *sc, *w1, *b1;
   float *fold, *w1t;     // layers >= 1: folded rank-8 algebra + k-major conv1x1 of the fused kernel
   float smooth;
+  // prompt fold (gemm2.cu / prompt_mid.cu), layers >= 1 at large batch: per-column constants of the fc2 and qkv epilogues,
+  // the sums / Gram matrix the statistics of x = v + U f + b1 need, and attn.proj's bias + conv1x1.bias
+  bool fold_on = false;
+  float *colw20 = nullptr, *fold2 = nullptr, *b_proj_r8 = nullptr, *b_qkv_r8 = nullptr, *cs_qkv_r8 = nullptr;
+  __half *wx_qkv = nullptr, *wx_proj = nullptr;      // extra k-block weights: W'U (2304, 64) and U (768, 64), 8 columns used
 };
 
 enum KernelClass { K_GEMM = 0, K_GEMM_HEAD, K_ATTN, K_PROMPT, K_NORM, K_CROP, K_IM2COL, K_HEAD_FINAL, K_NUM_CLASSES };
@@ -63,6 +68,9 @@ struct Engine {
   // activations
   __half *apatch, *xn, *dbuf, *qkv, *att, *hbuf, *feat16, *h1, *h2, *h3, *h4;
   float *E, *xA, *xB, *XD, *FV, *ce_prob, *ce_score, *feat32;
+  float* part = nullptr;                     // prompt fold: (6, B * 320, 20) row sums
+  __half* F16 = nullptr;                     // prompt fold: Fovea output per token row, fp16 (B * 320, 64), 8 columns used
+  float2* rowstat = nullptr;                 // prompt fold: (B * 320) (rstd, -mean * rstd) of norm1's input
   float2* lnstat = nullptr;           // LayerNorm fold: (24, B * 320) partial (sum, sum of squares) per row
   int *giA, *giB, *perm, *removed, *slot_of_pos, *ident, *err;
   // outputs / state
@@ -98,6 +106,8 @@ struct Engine {
   bool opt_zero_copy = true, opt_speculate = true;
   // VIPT_NO_LNFOLD=1 keeps every LayerNorm a separate pass (ln_rows_kernel); read once at engine creation, covered by a test
   bool opt_lnfold = true;
+  // VIPT_NO_PROMPT_FOLD=1 keeps the deep-prompt stage in prompt_coop_kernel at every layer; same rules
+  bool opt_promptfold = true;
   void plan_schedule();                    // CE schedule + which LayerNorms are folded (needs B, deep, num_sms)
   // zero-copy gather: the device-visible addresses of the B host frames travel as a kernel parameter
   static constexpr int kRoiSlots = 4;      // steps that may be enqueued before their results are collected

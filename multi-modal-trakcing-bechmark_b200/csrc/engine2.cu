@@ -46,7 +46,7 @@ int Engine::finalize_buffers() {
   AL(apatch, __half, 2 * R * 768);
   AL(E, float, 2 * R * 768);
   AL(xA, float, R * 768); AL(xB, float, R * 768);
-  AL(XD, float, R * 16); AL(FV, float, R * 8); AL(lnstat, float2, 24 * R);
+  AL(XD, float, R * 16); AL(FV, float, R * 8); AL(lnstat, float2, 24 * R); AL(part, float, 6 * R * 20); AL(F16, __half, R * 64); AL(rowstat, float2, R);
   AL(xn, __half, R * 768); AL(dbuf, __half, R * 768); AL(qkv, __half, R * 2304); AL(att, __half, R * 768); AL(hbuf, __half, R * 3072);
   AL(ce_prob, float, (size_t)B * kHeads * kLensX); AL(ce_score, float, 3 * RH);
   AL(feat16, __half, RH * 768); AL(feat32, float, R * 768);
@@ -67,6 +67,7 @@ int Engine::finalize_buffers() {
     CK(cudaMemset(err, 0, 4 * (1 + B)));
     RET(crop_prepare());
     CK(cudaMemset(removed, 0, 3 * RH * 4));
+    CK(cudaMemset(F16, 0, R * 64 * 2));      // columns 8..63 of the extra k-block stay zero
   }
   // ---- GEMM / attention plans
   const int M0 = B * kLensFull;
@@ -108,7 +109,12 @@ int Engine::finalize_buffers() {
     const int Ma = B * n_tok[i], Mm = B * n_mlp[i];
     // LayerNorm fold (gemm2.cu): the producer GEMM adds its branch to x in place and leaves x16 (in xn) + row statistics,
     // the consumer GEMM applies mean / rstd in its epilogue
-    if (L[i].fuse_ln1) {
+    if (PW[i].fold_on) {
+      // prompt fold (prompt_mid.cu): x16 = fp16(v), the rank-8 prompt update enters in the epilogue
+      RET(gemm2_plan(&g_qkv[i], xn, 768, L[i].w_qkv, 768, Ma, 2304, 768, EPI_LNFOLD_F16, qkv, 2304, PW[i].b_qkv_r8, num_sms / 2));
+      gemm2_set_lnfold(&g_qkv[i], rowstat, 0, PW[i].cs_qkv_r8, 1e-6f);      // final statistics from prompt_mid_kernel
+      RET(gemm2_set_kext(&g_qkv[i], F16, PW[i].wx_qkv));
+    } else if (L[i].fuse_ln1) {
       RET(gemm2_plan(&g_qkv[i], xn, 768, L[i].w_qkv, 768, Ma, 2304, 768, EPI_LNFOLD_F16, qkv, 2304, L[i].b_qkv, num_sms / 2));
       gemm2_set_lnfold(&g_qkv[i], lnstat, 24, L[i].cs_qkv, 1e-6f);
     } else {
@@ -118,7 +124,9 @@ int Engine::finalize_buffers() {
     // otherwise proj / fc2 write their branch output as fp16 (dbuf); the residual add is fused into the next
     // LayerNorm / prompt kernel, where it is coalesced
     if (L[i].fuse_ln2) {
-      RET(gemm2_plan_resid_stat(&g_proj[i], att, 768, L[i].w_proj, 768, Ma, 768, 768, x_cur, xn, L[i].b_proj, lnstat, num_sms / 2));
+      RET(gemm2_plan_resid_stat(&g_proj[i], att, 768, L[i].w_proj, 768, Ma, 768, 768, x_cur, xn,
+                                PW[i].fold_on ? PW[i].b_proj_r8 : L[i].b_proj, lnstat, num_sms / 2));
+      if (PW[i].fold_on) RET(gemm2_set_kext(&g_proj[i], F16, PW[i].wx_proj));    // x <- v + U f + b1 + proj(..)
       RET(gemm2_plan(&g_fc1[i], xn, 768, L[i].w_fc1, 768, Mm, 3072, 768, EPI_LNFOLD_GELU_F16, hbuf, 3072, L[i].b_fc1, num_sms / 2));
       gemm2_set_lnfold(&g_fc1[i], lnstat, 24, L[i].cs_fc1, 1e-6f);
     } else {
@@ -126,7 +134,9 @@ int Engine::finalize_buffers() {
       RET(plan_lin(&g_fc1[i], xn, 768, L[i].w_fc1, Mm, 3072, 768, EPI_GELU_F16, hbuf, L[i].b_fc1));
     }
     if (ce_keep[i]) { float* t = x_cur; x_cur = x_oth; x_oth = t; }
-    if (i + 1 < kDepth && L[i + 1].fuse_ln1) {
+    if (i + 1 < kDepth && PW[i + 1].fold_on) {
+      RET(gemm2_plan_resid_prompt(&g_fc2[i], hbuf, 3072, L[i].w_fc2, 3072, Mm, 768, 3072, x_cur, xn, L[i].b_fc2, PW[i + 1].colw20, part));
+    } else if (i + 1 < kDepth && L[i + 1].fuse_ln1) {
       RET(gemm2_plan_resid_stat(&g_fc2[i], hbuf, 3072, L[i].w_fc2, 3072, Mm, 768, 3072, x_cur, xn, L[i].b_fc2, lnstat, num_sms / 2));
     } else {
       RET(plan_lin(&g_fc2[i], hbuf, 3072, L[i].w_fc2, Mm, 768, 3072, EPI_BIAS_F16, dbuf, L[i].b_fc2));
@@ -199,7 +209,10 @@ int Engine::run_backbone_head(bool tracking, bool want_feat32, int debug_stop, c
   for (int i = 0; i < kDepth; ++i) {
     const int n = n_tok[i];
     if (i >= 1) {
-      if (deep) {
+      if (deep && PW[i].fold_on) {
+        // prompt fold: the 768-wide work is in the epilogues of fc2[i-1], qkv[i], proj[i]; this is the per-sequence part
+        LAUNCH(K_PROMPT, launch_prompt_mid(part, n, gi, FV, PW[i].fold, PW[i].fold2, F16, rowstat, B, kLensT, kLensFull, st));
+      } else if (deep) {
         // cooperative persistent kernel (prompt_coop.cu)
         LAUNCH(K_PROMPT, launch_prompt_coop(x, dbuf, n, gi, FV, XD, PW[i].wg_a, PW[i].fold, PW[i].w1t, PW[i].b1,
                                             L[i].ln1_g, L[i].ln1_b, xn, B, kLensT, kLensFull, num_sms, st));

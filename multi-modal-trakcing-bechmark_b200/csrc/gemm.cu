@@ -335,6 +335,7 @@ static int plan_common(GemmOp* op, const void* W, int64_t ldw, int64_t w_group_s
   op->p.conv_cb_per_tap = 0; op->p.conv_cin_stride = 0;
   op->p.stat_out = nullptr; op->p.stat_in = nullptr; op->p.stat_parts = 0; op->p.colsum = nullptr; op->p.ln_eps = 0.f;
   op->p.tail_from = 0; op->p.tail_split = 1;
+  op->p.colw = nullptr; op->p.part_out = nullptr; op->p.kext = 0;
   op->bn = bn; op->epi = epi;
   return VIPT_OK;
 }

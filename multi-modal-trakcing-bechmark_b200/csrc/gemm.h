@@ -20,6 +20,9 @@ enum GemmEpilogue {
   EPI_LNFOLD_F16 = 6,       // consumer: out fp16 = rstd * (acc - mean * colsum) + bias, W pre-scaled by the LayerNorm
                             // gain, bias = b + W beta                           (attn.qkv after norm1)
   EPI_LNFOLD_GELU_F16 = 7,  // consumer: the same followed by GELU              (mlp.fc1 after norm2)
+  // Deep-prompt stage carried by the GEMMs (gemm2.cu "prompt fold"; vit_ce_prompt.py:268-310):
+  EPI_RESID_PROMPT = 8,     // mlp.fc2: v = x + acc + bias in place, x16 = fp16(v), and per row and (tile, column half) the
+                            // 20 sums {v, v^2, v.wa_0..7, v.u_0..7, v.b1, -} the prompt block and norm1 need
 };
 
 struct GemmParams {
@@ -41,6 +44,13 @@ struct GemmParams {
   int stat_parts;
   const float* colsum;       // EPI_LNFOLD_*: (N) sum over k of the fp16 weight row
   float ln_eps;
+  // prompt fold, EPI_RESID_PROMPT: per-column constants (N, 20) floats = wa_0..7 (conv0_0 * gamma), u_0..7 (conv1x1), b1,
+  // 3 pad; streamed with the x slabs
+  const float* colw;
+  float* part_out;           // EPI_RESID_PROMPT: (2 * N / 256, M, 20) partial sums
+  // one extra k-block of 64 after the K / 64 regular ones, from the maps tmAx (M, 64) / tmBx (N, 64): a rank-<=64 update
+  // A W^T + Ax Wx^T on the tensor pipe (prompt fold: Ax = the Fovea output f per row, Wx = W'U resp. U)
+  int kext;
   // 2-CTA kernel: tiles >= tail_from (the last, partial round of the persistent loop) are cut into tail_split strips
   int tail_from, tail_split;
 };
@@ -48,6 +58,7 @@ struct GemmParams {
 struct GemmOp {
   CUtensorMap tmA, tmB, tmC;   // tmC: output map of the 2-CTA kernel's TMA-store epilogue
   CUtensorMap tmB2;            // 2-CTA kernel: weight map with the box of a tail strip
+  CUtensorMap tmAx, tmBx;      // 2-CTA kernel, kext: the extra k-block
   CUtensorMap tmC2;            // EPI_RESID_STAT: fp16 copy of the updated rows (tmC = the fp32 rows, loaded and stored)
   GemmParams p;
   int bn, epi;
@@ -73,7 +84,13 @@ int gemm2_launch(const GemmOp& op, int num_sms, cudaStream_t st);
 // LayerNorm fold, producer: x (M, N) fp32 ld N updated in place, x16 (M, N) fp16, stat_out (N / 32, M)
 int gemm2_plan_resid_stat(GemmOp* op, const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, float* x,
                           void* x16, const float* bias, float2* stat_out, int num_clusters = 0);
-// LayerNorm fold, consumer: gemm2_plan(.., epi = EPI_LNFOLD_*, ..) followed by this
+// prompt fold
+int gemm2_plan_resid_prompt(GemmOp* op, const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, float* x,
+                            void* x16, const float* bias, const float* colw20, float* part_out);
+// extra k-block (any 2-CTA plan with 256-wide tiles): Ax (M, 64) fp16, Wx (N, 64) fp16, both row-major with ld 64
+int gemm2_set_kext(GemmOp* op, const void* Ax, const void* Wx);
+// LayerNorm fold, consumer: gemm2_plan(.., epi = EPI_LNFOLD_*, ..) followed by this; stat_parts = 0: stat_in (M) holds the
+// final (rstd, -mean * rstd) of every row
 void gemm2_set_lnfold(GemmOp* op, const float2* stat_in, int stat_parts, const float* colsum, float ln_eps);
 int make_tmap_ex(CUtensorMap* out, int dtype_f32, int swizzle_bytes, const void* base, int rank, const uint64_t* dims,
                  const uint64_t* strides_bytes, const uint32_t* box);

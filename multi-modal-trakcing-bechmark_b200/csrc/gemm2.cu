@@ -16,14 +16,23 @@
 // LayerNorm fold (north star (b): "GEMMs ... with LayerNorm, GELU and bias fused in"; reference sites
 // ViPT/lib/models/layers/attn_blocks.py:94,103).  blocks[i].norm2 between attn.proj and mlp.fc1 (and, without deep
 // prompts, norm1 between mlp.fc2 and the next attn.qkv) is not a pass over the residual stream any more:
-//   producer  EPI_RESID_STAT   x <- x + acc + bias  in fp32, IN PLACE through one fp32 tensor map (a fourth warp
-//             streams the x slabs of the tile in through a 3-deep ring while the main loop runs; the epilogue adds,
-//             writes the fp32 slab and an fp16 copy x16 back with TMA stores) and every thread -- it owns one row of
-//             the tile -- keeps (sum, sum of squares) of its 128 columns: stat[(2 tile_n + half)][row]
+//   producer  EPI_RESID_STAT   x <- x + acc + bias  in fp32, IN PLACE through one fp32 tensor map (the fourth warp
+//             streams the x slabs of the tile in through a ring while the main loop runs; the epilogue adds, writes
+//             the fp32 slab and an fp16 copy x16 back with TMA stores) and every thread -- it owns one row of the
+//             tile -- keeps (sum, sum of squares) of its columns
 //   consumer  EPI_LNFOLD_*     A = x16, W' = fp16(gamma * W):   LN(x) W^T + b = rstd (x16 W'^T - mean colsum(W')) + (b + W beta)
-//             mean / rstd per row from the partial sums (per thread: its row), two FMAs per element
+//             mean / rstd per row, two FMAs per element; the fourth warp prepares them one tile ahead
 // The fp16 rounding of x instead of LN(x) gives the same operand error as long as |mean| is not large against the
 // standard deviation of a row (measured on the synthetic weight sets: 2.9e-4 relative either way).
+//
+// Prompt fold (vit_ce_prompt.py:268-310; prompt_mid.cu has the whole picture): the deep-prompt stage of block i is
+//   mlp.fc2 of block i-1, EPI_RESID_PROMPT: the residual epilogue also keeps, per row, the 17 dot products of
+//             v = x + fc2(..) with conv0_0 * gamma (8), conv1x1 (8) and conv1x1.bias (the constants of a step's 32
+//             columns travel with its x slab), so x0 = conv0_0(prompt_norms(v)) and the statistics of
+//             x = v + U f + b1 need no pass over v
+//   attn.qkv / attn.proj of block i: the rank-8 update U f enters as ONE EXTRA K-BLOCK (kext): Ax = f per row
+//             (fp16, 8 of 64 columns used), Wx = W'U resp. U -- an eighth of a k-block of tensor work instead of 8 FMAs
+//             per element in the epilogue (measured: +21 us per qkv launch in the epilogue form)
 #include <stdlib.h>
 
 #include "gemm.h"
@@ -37,24 +46,28 @@ constexpr int BK = 64;
 constexpr int kSlabCols = 64;                        // epilogue slab: 128 rows x 64 fp16 = 16 KB, SW128
 constexpr int kSlabBytes = BM * kSlabCols * 2;
 constexpr int kABytes = BM * BK * 2;
-constexpr int kThreads = 384;          // warp 0 TMA, 1 MMA, 2 TMEM alloc, 4..11 epilogue (2 per TMEM lane group)
-constexpr int kEpiThreads = 256;
-// BN = columns per pair tile: 256, or 128 for the N = 768 layers (proj, fc2), whose 3 x tiles_m grid of
-// 256-wide tiles leaves the last wave of the persistent loop a third empty
-constexpr int kResidRing = 3;      // EPI_RESID_STAT: fp32 slabs of x in flight towards the epilogue
-template <int BN, int EPI>
+constexpr int kThreads = 384;          // warp 0 TMA, 1 MMA, 2 TMEM alloc, 3 epilogue feeder, 4..11 epilogue (2 per TMEM lane group)
+constexpr int kRingMax = 3;            // residual epilogues: x slabs in flight towards the epilogue (barrier slots)
+__host__ __device__ constexpr bool epi_resid(int epi) { return epi == EPI_RESID_STAT || epi == EPI_RESID_PROMPT; }
+constexpr int kColwStep = 32 * 20 * 4;     // EPI_RESID_PROMPT: the 20 constants of a step's 32 columns travel with its x slab
+// BN = columns per pair tile: 256, or 128 for N % 256 != 0.
+// DEEPK (residual epilogues only): K >= 2048.  The main loop then needs its 5 stages (with 3 the fc2-sized GEMM ran at
+// 51 % tensor activity, waiting for operands) and leaves the epilogue ~13 us per tile, so the epilogue gets the small
+// configuration: 2 x slabs in flight, ONE output slab.  Shallow K (attn.proj): 3 stages, 3 slabs in, 2 out.
+template <int BN, int EPI, int DEEPK>
 struct Cfg {
-  static constexpr bool kResid = EPI == EPI_RESID_STAT;
-  static constexpr int kStages = kResid ? 3 : (BN == 256 ? 5 : 6);
+  static constexpr bool kResid = epi_resid(EPI);
+  static constexpr int kStages = kResid ? (DEEPK ? 5 : 3) : (BN == 256 ? 5 : 6);
   static constexpr int kBBytes = (BN / 2) * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  // 4 staging slabs: 2 for fp16 outputs (double-buffered 64-column slabs; the LayerNorm-fold consumers keep the column
-  // sums in the third), 4 for fp32 outputs (two 32-column slabs per step).  EPI_RESID_STAT: 3 fp32 slabs in (128 rows x
-  // 32 columns), 3 fp32 slabs out, 3 half-size fp16 slabs out (a store may still be reading its slab while the next
-  // step is staged: with two slabs every step waited for the previous store to drain, the largest stall of the kernel).
-  static constexpr int kSlabs = kResid ? kResidRing + 5 : 4;
-  static constexpr int kSmemBytes =
-      1024 + kStages * kStageBytes + kSlabs * kSlabBytes + BN * 4 + (2 * kStages + 4 + 2 * kResidRing) * 8 + 16;
+  static constexpr int kIn = DEEPK ? 2 : 3, kOut = DEEPK ? 1 : 2;
+  // per ring slot; a multiple of 1024 so that every x slab keeps the 1024-byte alignment its 128-byte swizzle assumes
+  static constexpr int kInBytes = kSlabBytes + (EPI == EPI_RESID_PROMPT ? (kColwStep + 1023) / 1024 * 1024 : 0);
+  static constexpr int kOutBytes = kSlabBytes + kSlabBytes / 2;                               // fp32 slab + fp16 slab
+  // plain epilogues: 4 staging slabs, 2 for fp16 outputs (double-buffered 64-column slabs; the LayerNorm-fold consumers
+  // keep column sums and row statistics in the third), 4 for fp32 outputs (two 32-column slabs per step)
+  static constexpr int kEpiBytes = kResid ? kIn * kInBytes + kOut * kOutBytes : 4 * kSlabBytes;
+  static constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kEpiBytes + BN * 4 + (2 * kStages + 4 + 2 * kRingMax) * 8 + 16;
 };
 }  // namespace g2
 
@@ -120,29 +133,35 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
       : "memory");
 }
 
-template <int EPI, int BN>
+struct Gemm2Maps {
+  CUtensorMap A, B, C, C2, B2, Ax, Bx;
+};
+
+template <int EPI, int BN, int DEEPK>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(g2::kThreads, 1)
-gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-             const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmC2,
-             const __grid_constant__ CUtensorMap tmB2, GemmParams p) {
+gemm2_kernel(const __grid_constant__ Gemm2Maps tm, GemmParams p) {
   using namespace g2;
-  constexpr int kStages = Cfg<BN, EPI>::kStages, kStageBytes = Cfg<BN, EPI>::kStageBytes;
-  constexpr bool kResid = EPI == EPI_RESID_STAT;
+  using C = Cfg<BN, EPI, DEEPK>;
+  constexpr int kStages = C::kStages, kStageBytes = C::kStageBytes;
+  constexpr bool kResid = epi_resid(EPI);
+  constexpr bool kPrompt = EPI == EPI_RESID_PROMPT;          // residual + the sums of the prompt block
   constexpr bool kFold = EPI == EPI_LNFOLD_F16 || EPI == EPI_LNFOLD_GELU_F16;
+  constexpr int kIn = C::kIn, kOut = C::kOut, kInBytes = C::kInBytes, kOutBytes = C::kOutBytes;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* tiles = smem;
-  uint8_t* slab = smem + kStages * kStageBytes;            // 2 x 16 KB output staging (TMA store source)
-  float* bias_s = reinterpret_cast<float*>(slab + Cfg<BN, EPI>::kSlabs * kSlabBytes);
+  uint8_t* slab = smem + kStages * kStageBytes;            // epilogue staging (TMA store sources; residual: x slabs in)
+  uint8_t* out_slab = slab + kIn * kInBytes;               // kResid: kOut x (fp32 slab, fp16 half slab)
+  float* bias_s = reinterpret_cast<float*>(slab + C::kEpiBytes);
   float* cs_s = reinterpret_cast<float*>(slab + 2 * kSlabBytes);      // kFold: column sums (fp16 outputs use 2 slabs)
   float2* rowstat_s = reinterpret_cast<float2*>(slab + 2 * kSlabBytes + 4096);   // kFold: [2][128] (rstd, -mean * rstd)
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(bias_s + BN);
   uint64_t* empty_bar = full_bar + kStages;
   uint64_t* tfull_bar = empty_bar + kStages;
   uint64_t* tempty_bar = tfull_bar + 2;
-  uint64_t* rfull_bar = tempty_bar + 2;                               // kResid: x slab ring
-  uint64_t* rempty_bar = rfull_bar + kResidRing;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(rempty_bar + kResidRing);
+  uint64_t* rfull_bar = tempty_bar + 2;                               // kResid: x slab ring; kFold: row statistics slots
+  uint64_t* rempty_bar = rfull_bar + kRingMax;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(rempty_bar + kRingMax);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -156,7 +175,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   // cut into tail_split column strips (unit u >= tail_from: tile tail_from + (u - tail_from) / split, strip
   // (u - tail_from) % split).  Strips use the same k order, so results do not depend on the split.
   const int num_tiles = p.tail_from + (tiles_m * tiles_n - p.tail_from) * p.tail_split;
-  const int num_kb = p.K / BK;
+  const int num_kb = p.K / BK + p.kext;                  // kext: one more k-block from the maps Ax / Bx
   struct Unit { int tm, n0, width; };
   auto unit_of = [&](int u) -> Unit {
     int tile = u, strip = 0, width = BN;
@@ -170,12 +189,13 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   };
 
   if (threadIdx.x == 0) {
-    tma_prefetch_desc(&tmA);
-    tma_prefetch_desc(&tmB);
-    tma_prefetch_desc(&tmC);
-    if (kResid) tma_prefetch_desc(&tmC2);
-    if (p.tail_split > 1) tma_prefetch_desc(&tmB2);
-    for (int s = 0; s < kResidRing; ++s) {
+    tma_prefetch_desc(&tm.A);
+    tma_prefetch_desc(&tm.B);
+    tma_prefetch_desc(&tm.C);
+    if (kResid) tma_prefetch_desc(&tm.C2);
+    if (p.tail_split > 1) tma_prefetch_desc(&tm.B2);
+    if (p.kext) { tma_prefetch_desc(&tm.Ax); tma_prefetch_desc(&tm.Bx); }
+    for (int s = 0; s < kRingMax; ++s) {
       mbar_init(&rfull_bar[s], 1);
       mbar_init(&rempty_bar[s], 8);   // 8 epilogue warps
     }
@@ -209,7 +229,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     uint32_t ph = 0;
     for (int t = cluster_id; t < num_tiles; t += num_clusters) {
       const Unit un = unit_of(t);
-      const int tm = un.tm;
+      const int tm_ = un.tm;
       const bool strip = un.width != BN;
       const uint32_t tx_bytes = 2 * (kABytes + (un.width / 2) * BK * 2);
       for (int kb = 0; kb < num_kb; ++kb) {
@@ -217,15 +237,22 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         uint8_t* a_dst = tiles + s * kStageBytes;
         uint8_t* b_dst = a_dst + kABytes;
         const uint32_t bar = mapa_cta(smem_u32(&full_bar[s]), 0);
+        const bool ext = p.kext && kb == num_kb - 1;
         if (elect_one()) {
-          if (leader) mbar_expect_tx(&full_bar[s], tx_bytes);
-          if (p.conv_cb_per_tap) {    // implicit 3x3 conv: the pair tile is one sequence's 16 x 16 map, 8 rows per CTA
-            const int tap = kb / p.conv_cb_per_tap, cb = kb % p.conv_cb_per_tap;
-            tma_load_4d_2cta(a_dst, &tmA, bar, cb * BK, tap % 3 - 1, (int)rank * 8 + tap / 3 - 1, tm);
+          // (the extra k-block always loads the full 128-row weight box: a strip's MMA reads its first rows only)
+          if (leader) mbar_expect_tx(&full_bar[s], ext ? 2 * kStageBytes : tx_bytes);
+          if (ext) {
+            tma_load_3d_2cta(a_dst, &tm.Ax, bar, 0, tm_ * 2 * BM + (int)rank * BM, 0);
+            tma_load_3d_2cta(b_dst, &tm.Bx, bar, 0, un.n0 + (int)rank * (un.width / 2), 0);
           } else {
-            tma_load_3d_2cta(a_dst, &tmA, bar, kb * BK, tm * 2 * BM + (int)rank * BM, 0);
+            if (p.conv_cb_per_tap) {    // implicit 3x3 conv: the pair tile is one sequence's 16 x 16 map, 8 rows per CTA
+              const int tap = kb / p.conv_cb_per_tap, cb = kb % p.conv_cb_per_tap;
+              tma_load_4d_2cta(a_dst, &tm.A, bar, cb * BK, tap % 3 - 1, (int)rank * 8 + tap / 3 - 1, tm_);
+            } else {
+              tma_load_3d_2cta(a_dst, &tm.A, bar, kb * BK, tm_ * 2 * BM + (int)rank * BM, 0);
+            }
+            tma_load_3d_2cta(b_dst, strip ? &tm.B2 : &tm.B, bar, kb * BK, un.n0 + (int)rank * (un.width / 2), 0);
           }
-          tma_load_3d_2cta(b_dst, strip ? &tmB2 : &tmB, bar, kb * BK, un.n0 + (int)rank * (un.width / 2), 0);
         }
         __syncwarp();
         if (++s == kStages) { s = 0; ph ^= 1; }
@@ -266,44 +293,53 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     // ------------------------------------------------ row statistics (both CTAs), one tile ahead of the epilogue: the
     // partial sums of this CTA's 128 rows -> (rstd, -mean * rstd) in shared memory.  (Read by the epilogue threads
     // themselves, the global-load latency sat on every tile's critical path: fc1 69.6 -> 94.2 us.)
-    const float inv_k = 1.f / (float)p.K;
+    const float inv_k = 1.f / (float)(p.K);
     int it = 0;
     for (int t = cluster_id; t < num_tiles; t += num_clusters, ++it) {
       const int row0 = unit_of(t).tm * 2 * BM + (int)rank * BM;
       const int slot = it & 1;
       mbar_wait(&rempty_bar[slot], ((it >> 1) & 1) ^ 1);
-      // 4 rows per lane; the partial sums of a row are added in part order (the result does not depend on the
-      // schedule), the loads go out in batches of 8 parts x 4 rows so that their latencies overlap
-      float s1[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f};
-      for (int q0 = 0; q0 < p.stat_parts; q0 += 8) {
-        float2 st[4][8];
+      if (p.stat_parts == 0) {       // final statistics (prompt fold: prompt_mid_kernel wrote them)
 #pragma unroll
-        for (int i = 0; i < 4; ++i)
+        for (int i = 0; i < 4; ++i) {
+          const int rr = row0 + i * 32 + lane;
+          rowstat_s[slot * BM + i * 32 + lane] = rr < p.M ? __ldg(p.stat_in + rr) : make_float2(0.f, 0.f);
+        }
+      } else {
+        // 4 rows per lane; the partial sums of a row are added in part order (the result does not depend on the
+        // schedule), the loads go out in batches of 8 parts x 4 rows so that their latencies overlap
+        float s1[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f};
+        for (int q0 = 0; q0 < p.stat_parts; q0 += 8) {
+          float2 st[4][8];
 #pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            const int rr = row0 + i * 32 + lane;
-            st[i][u] = (q0 + u < p.stat_parts && rr < p.M) ? __ldg(p.stat_in + (size_t)(q0 + u) * p.M + rr) : make_float2(0.f, 0.f);
-          }
+          for (int i = 0; i < 4; ++i)
 #pragma unroll
-        for (int i = 0; i < 4; ++i)
+            for (int u = 0; u < 8; ++u) {
+              const int rr = row0 + i * 32 + lane;
+              st[i][u] = (q0 + u < p.stat_parts && rr < p.M) ? __ldg(p.stat_in + (size_t)(q0 + u) * p.M + rr) : make_float2(0.f, 0.f);
+            }
 #pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            s1[i] += st[i][u].x;
-            s2[i] += st[i][u].y;
-          }
-      }
+          for (int i = 0; i < 4; ++i)
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const float mean = s1[i] * inv_k;
-        const float rs = rsqrtf(fmaxf(fmaf(-mean, mean, s2[i] * inv_k), 0.f) + p.ln_eps);
-        rowstat_s[slot * BM + i * 32 + lane] = make_float2(rs, -mean * rs);       // (rows >= M: never stored)
+            for (int u = 0; u < 8; ++u) {
+              s1[i] += st[i][u].x;
+              s2[i] += st[i][u].y;
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float mean = s1[i] * inv_k;
+          const float rs = rsqrtf(fmaxf(fmaf(-mean, mean, s2[i] * inv_k), 0.f) + p.ln_eps);
+          rowstat_s[slot * BM + i * 32 + lane] = make_float2(rs, -mean * rs);       // (rows >= M: never stored)
+        }
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(&rfull_bar[slot]);
     }
   } else if (kResid && warp == 3) {
     // ------------------------------------------------ x slab producer (both CTAs): the fp32 rows this CTA's tile updates,
-    // 32 columns at a time, in the order the epilogue consumes them; runs ahead of the epilogue by the ring depth
+    // 32 columns at a time, in the order the epilogue consumes them (kPrompt: with the 20 constants of those columns);
+    // runs ahead of the epilogue by the ring depth
     int rs = 0;
     uint32_t rph = 0;
     for (int t = cluster_id; t < num_tiles; t += num_clusters) {
@@ -313,11 +349,15 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
       for (int j = 0; j < un.width / 32; ++j) {
         mbar_wait(&rempty_bar[rs], rph ^ 1);
         if (elect_one()) {
-          mbar_expect_tx(&rfull_bar[rs], kSlabBytes);
-          tma_load_3d(slab + rs * kSlabBytes, &tmC, &rfull_bar[rs], n0 + j * 32, row0, 0);
+          mbar_expect_tx(&rfull_bar[rs], kSlabBytes + (kPrompt ? kColwStep : 0));
+          tma_load_3d(slab + rs * kInBytes, &tm.C, &rfull_bar[rs], n0 + j * 32, row0, 0);
+          if (kPrompt)
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         ::"r"(smem_u32(slab + rs * kInBytes + kSlabBytes)), "l"(p.colw + (size_t)(n0 + j * 32) * 20),
+                           "r"(kColwStep), "r"(smem_u32(&rfull_bar[rs])) : "memory");
         }
         __syncwarp();
-        if (++rs == kResidRing) { rs = 0; rph ^= 1; }
+        if (++rs == kIn) { rs = 0; rph ^= 1; }
       }
     }
   } else if (warp >= 4) {
@@ -331,7 +371,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     int rs = 0;                  // kResid: x slab ring position
     uint32_t rph = 0;
     int it = 0;                  // kFold: tile counter (row statistics slots)
-    int ob = 0;                  // kResid: output slab (0..2), runs on across tiles
+    int ob = 0;                  // kResid: output slab, runs on across tiles
     float next_bias = 0.f, next_cs = 0.f;      // bias / column sum of column `et` of the next tile
     if (cluster_id < num_tiles) {
       const Unit nx = unit_of(cluster_id);
@@ -342,10 +382,10 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     }
     for (int t = cluster_id; t < num_tiles; t += num_clusters, ++it) {
       const Unit un = unit_of(t);
-      const int tm = un.tm;
+      const int tm_ = un.tm;
       const int n0 = un.n0;
       const int n_slabs = un.width / kSlabCols;
-      const int row0 = tm * 2 * BM + (int)rank * BM;           // first row of this CTA's 128 x 256 tile
+      const int row0 = tm_ * 2 * BM + (int)rank * BM;          // first row of this CTA's 128 x 256 tile
       const int r = we * 32 + lane;                            // row within the tile == TMEM lane
       // (bias_s of the previous tile was last read before that tile's final slab barrier.)  The values were fetched
       // while the previous tile was in the epilogue: read here, the global-load latency sat on every tile's critical
@@ -378,13 +418,18 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         // x <- x + acc + bias, 32 columns per step: this warp set's threads take 16 of them (hh)
         const uint32_t taddr0 = tmem_base + as * BN + hh * 16 + ((uint32_t)(we * 32) << 16);
         float s1 = 0.f, s2 = 0.f;
+        uint64_t pa[8];            // kPrompt: (v.wa_0, v.wa_1) .. (v.wa_6, v.wa_7), (v.u_0, v.u_1) .. (v.u_6, v.u_7)
+        float pe = 0.f;            // kPrompt: v.b1
+#pragma unroll
+        for (int k = 0; k < 8; ++k) pa[k] = 0ull;
         uint32_t v[16];
         tmem_ld16(taddr0, v);
         const int n_steps = un.width / 32;
 #pragma unroll 1
         for (int j = 0; j < n_steps; ++j) {
           mbar_wait(&rfull_bar[rs], rph);
-          const uint32_t in_row = smem_u32(slab + rs * kSlabBytes) + r * 128;
+          const uint32_t in_base = smem_u32(slab + rs * kInBytes);
+          const uint32_t in_row = in_base + r * 128;
           const uint32_t brow = bias_u32 + (j * 32 + hh * 16) * 4;
           float f[16];
           tmem_ld_wait();
@@ -403,42 +448,73 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
             s1 += f[k];
             s2 = fmaf(f[k], f[k], s2);
           }
-          if (j & 1) {           // a 64-column group is complete: part 2 * group + hh (this thread's 32 of its columns)
-            if (row0 + r < p.M) p.stat_out[(size_t)(((n0 >> 6) + (j >> 1)) * 2 + hh) * p.M + row0 + r] = make_float2(s1, s2);
+          if (kPrompt) {         // 17 more row sums: packed FMAs on the (wa, u) pairs of the column, broadcast from smem
+            const uint32_t wrow = in_base + kSlabBytes + hh * 16 * 80;
+#pragma unroll
+            for (int c = 0; c < 16; ++c) {
+              const uint64_t ff = pk2(f[c], f[c]);
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                const float4 w = lds128f(wrow + c * 80 + q * 16);
+                pa[q * 2] = fma2(pk2(w.x, w.y), ff, pa[q * 2]);
+                pa[q * 2 + 1] = fma2(pk2(w.z, w.w), ff, pa[q * 2 + 1]);
+              }
+              float b1c;
+              asm volatile("ld.shared.f32 %0, [%1];" : "=f"(b1c) : "r"(wrow + c * 80 + 64) : "memory");
+              pe = fmaf(b1c, f[c], pe);
+            }
+          } else if (j & 1) {    // a 64-column group is complete: part 2 * group + hh (this thread's 32 of its columns)
+            if (p.stat_out && row0 + r < p.M)
+              p.stat_out[(size_t)(((n0 >> 6) + (j >> 1)) * 2 + hh) * p.M + row0 + r] = make_float2(s1, s2);
             s1 = 0.f;
             s2 = 0.f;
           }
-          const uint32_t o32 = smem_u32(slab + (kResidRing + ob) * kSlabBytes) + r * 128;
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&rempty_bar[rs]);         // the x slab (and its constants) are consumed
+          if (++rs == kIn) { rs = 0; rph ^= 1; }
+          if (kOut == 1) {       // single output slab: its previous store must have drained before anybody writes it
+            if (et == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+          }
+          const uint32_t o32 = smem_u32(out_slab + ob * kOutBytes) + r * 128;
 #pragma unroll
           for (int q = 0; q < 4; ++q)
             sts128(o32 + (((hh * 4 + q) ^ (r & 7)) * 16), __float_as_uint(f[q * 4 + 0]), __float_as_uint(f[q * 4 + 1]),
                    __float_as_uint(f[q * 4 + 2]), __float_as_uint(f[q * 4 + 3]));
           // fp16 copy: 128 rows x 32 columns = 64-byte rows, 64-byte swizzle (16-byte chunk ^= (row / 2) % 4)
-          const uint32_t o16 = smem_u32(slab + (kResidRing + 3) * kSlabBytes) + ob * (kSlabBytes / 2) + r * 64;
+          const uint32_t o16 = smem_u32(out_slab + ob * kOutBytes + kSlabBytes) + r * 64;
 #pragma unroll
           for (int q = 0; q < 2; ++q)
             sts128(o16 + (((hh * 2 + q) ^ ((r >> 1) & 3)) * 16), pack_op2(f[q * 8 + 0], f[q * 8 + 1]),
                    pack_op2(f[q * 8 + 2], f[q * 8 + 3]), pack_op2(f[q * 8 + 4], f[q * 8 + 5]), pack_op2(f[q * 8 + 6], f[q * 8 + 7]));
           fence_proxy_async_smem();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&rempty_bar[rs]);         // the x slab is consumed
-          if (++rs == kResidRing) { rs = 0; rph ^= 1; }
-          // the slab the NEXT step writes was read by the store issued two steps ago: at most one store may be pending
-          if (et == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+          // two output slabs: before the barrier the issuing thread makes sure the previous store has drained the slab
+          // the next step writes
+          if (kOut == 2 && et == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
           asm volatile("bar.sync 1, 256;" ::: "memory");
           if (et == 0) {
             asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
-                         ::"l"(reinterpret_cast<uint64_t>(&tmC)), "r"(smem_u32(slab + (kResidRing + ob) * kSlabBytes)),
+                         ::"l"(reinterpret_cast<uint64_t>(&tm.C)), "r"(smem_u32(out_slab + ob * kOutBytes)),
                            "r"(n0 + j * 32), "r"(row0), "r"(0)
                          : "memory");
             asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
-                         ::"l"(reinterpret_cast<uint64_t>(&tmC2)),
-                           "r"(smem_u32(slab + (kResidRing + 3) * kSlabBytes) + ob * (kSlabBytes / 2)), "r"(n0 + j * 32),
-                           "r"(row0), "r"(0)
+                         ::"l"(reinterpret_cast<uint64_t>(&tm.C2)), "r"(smem_u32(out_slab + ob * kOutBytes + kSlabBytes)),
+                           "r"(n0 + j * 32), "r"(row0), "r"(0)
                          : "memory");
             asm volatile("cp.async.bulk.commit_group;" ::: "memory");
           }
-          if (++ob == 3) ob = 0;
+          if (kOut == 2) ob ^= 1;
+        }
+        if (kPrompt && row0 + r < p.M) {       // 20 floats per row and (tile, half): s1, s2, v.wa_0..7, v.u_0..7, v.b1, 0
+          float4* po = reinterpret_cast<float4*>(p.part_out + ((size_t)((n0 / BN) * 2 + hh) * p.M + row0 + r) * 20);
+          float a[16];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) upk2(pa[k], a[2 * k], a[2 * k + 1]);
+          po[0] = make_float4(s1, s2, a[0], a[1]);
+          po[1] = make_float4(a[2], a[3], a[4], a[5]);
+          po[2] = make_float4(a[6], a[7], a[8], a[9]);
+          po[3] = make_float4(a[10], a[11], a[12], a[13]);
+          po[4] = make_float4(a[14], a[15], pe, 0.f);
         }
         tc_fence_before();
         __syncwarp();
@@ -508,12 +584,12 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
 #pragma unroll
             for (int h2 = 0; h2 < 2; ++h2)
               asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
-                           ::"l"(reinterpret_cast<uint64_t>(&tmC)), "r"(smem_u32(slab + ((sl & 1) * 2 + h2) * kSlabBytes)),
+                           ::"l"(reinterpret_cast<uint64_t>(&tm.C)), "r"(smem_u32(slab + ((sl & 1) * 2 + h2) * kSlabBytes)),
                              "r"(n0 + sl * kSlabCols + h2 * 32), "r"(row0), "r"(0)
                            : "memory");
           } else {
             asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
-                         ::"l"(reinterpret_cast<uint64_t>(&tmC)), "r"(smem_u32(buf)), "r"(n0 + sl * kSlabCols), "r"(row0),
+                         ::"l"(reinterpret_cast<uint64_t>(&tm.C)), "r"(smem_u32(buf)), "r"(n0 + sl * kSlabCols), "r"(row0),
                          "r"(0)
                          : "memory");
           }
@@ -537,12 +613,13 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   }
 }
 
-template <int EPI, int BN>
+template <int EPI, int BN, int DEEPK>
 static int launch2_t(const GemmOp& op, int num_sms, cudaStream_t st) {
+  using C = g2::Cfg<BN, EPI, DEEPK>;
+  static_assert(C::kSmemBytes <= 232448, "shared memory budget");
   static bool attr_set = false;
   if (!attr_set) {
-    if (cudaFuncSetAttribute(gemm2_kernel<EPI, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             g2::Cfg<BN, EPI>::kSmemBytes) != cudaSuccess)
+    if (cudaFuncSetAttribute(gemm2_kernel<EPI, BN, DEEPK>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes) != cudaSuccess)
       return VIPT_ERR_LAUNCH;
     attr_set = true;
   }
@@ -550,23 +627,29 @@ static int launch2_t(const GemmOp& op, int num_sms, cudaStream_t st) {
   int grid = 2 * tiles;
   const int cap = num_sms & ~1;
   if (grid > cap) grid = cap;
-  return launch_pdl(gemm2_kernel<EPI, BN>, grid, g2::kThreads, g2::Cfg<BN, EPI>::kSmemBytes, st, op.tmA, op.tmB, op.tmC, op.tmC2,
-                    op.tmB2, op.p) == cudaSuccess
-             ? VIPT_OK
-             : VIPT_ERR_LAUNCH;
+  Gemm2Maps tm;
+  tm.A = op.tmA; tm.B = op.tmB; tm.C = op.tmC; tm.C2 = op.tmC2; tm.B2 = op.tmB2; tm.Ax = op.tmAx; tm.Bx = op.tmBx;
+  return launch_pdl(gemm2_kernel<EPI, BN, DEEPK>, grid, g2::kThreads, C::kSmemBytes, st, tm, op.p) == cudaSuccess ? VIPT_OK
+                                                                                                                  : VIPT_ERR_LAUNCH;
 }
 
 int gemm2_launch(const GemmOp& op, int num_sms, cudaStream_t st) {
   const bool narrow = op.bn == 640;
+  const bool deep = op.p.K >= 2048;
   switch (op.epi) {
-    case EPI_BIAS_F16: return narrow ? launch2_t<EPI_BIAS_F16, 128>(op, num_sms, st) : launch2_t<EPI_BIAS_F16, 256>(op, num_sms, st);
-    case EPI_GELU_F16: return narrow ? launch2_t<EPI_GELU_F16, 128>(op, num_sms, st) : launch2_t<EPI_GELU_F16, 256>(op, num_sms, st);
-    case EPI_RELU_F16: return narrow ? launch2_t<EPI_RELU_F16, 128>(op, num_sms, st) : launch2_t<EPI_RELU_F16, 256>(op, num_sms, st);
-    case EPI_BIAS_F32: return narrow ? launch2_t<EPI_BIAS_F32, 128>(op, num_sms, st) : launch2_t<EPI_BIAS_F32, 256>(op, num_sms, st);
-    // LayerNorm fold: 256-wide pair tiles only
-    case EPI_RESID_STAT: return narrow ? VIPT_ERR_ARG : launch2_t<EPI_RESID_STAT, 256>(op, num_sms, st);
-    case EPI_LNFOLD_F16: return narrow ? VIPT_ERR_ARG : launch2_t<EPI_LNFOLD_F16, 256>(op, num_sms, st);
-    case EPI_LNFOLD_GELU_F16: return narrow ? VIPT_ERR_ARG : launch2_t<EPI_LNFOLD_GELU_F16, 256>(op, num_sms, st);
+    case EPI_BIAS_F16: return narrow ? launch2_t<EPI_BIAS_F16, 128, 0>(op, num_sms, st) : launch2_t<EPI_BIAS_F16, 256, 0>(op, num_sms, st);
+    case EPI_GELU_F16: return narrow ? launch2_t<EPI_GELU_F16, 128, 0>(op, num_sms, st) : launch2_t<EPI_GELU_F16, 256, 0>(op, num_sms, st);
+    case EPI_RELU_F16: return narrow ? launch2_t<EPI_RELU_F16, 128, 0>(op, num_sms, st) : launch2_t<EPI_RELU_F16, 256, 0>(op, num_sms, st);
+    case EPI_BIAS_F32: return narrow ? launch2_t<EPI_BIAS_F32, 128, 0>(op, num_sms, st) : launch2_t<EPI_BIAS_F32, 256, 0>(op, num_sms, st);
+    // LayerNorm / prompt fold: 256-wide pair tiles only
+    case EPI_RESID_STAT:
+      if (narrow) return VIPT_ERR_ARG;
+      return deep ? launch2_t<EPI_RESID_STAT, 256, 1>(op, num_sms, st) : launch2_t<EPI_RESID_STAT, 256, 0>(op, num_sms, st);
+    case EPI_RESID_PROMPT:
+      if (narrow) return VIPT_ERR_ARG;
+      return deep ? launch2_t<EPI_RESID_PROMPT, 256, 1>(op, num_sms, st) : launch2_t<EPI_RESID_PROMPT, 256, 0>(op, num_sms, st);
+    case EPI_LNFOLD_F16: return narrow ? VIPT_ERR_ARG : launch2_t<EPI_LNFOLD_F16, 256, 0>(op, num_sms, st);
+    case EPI_LNFOLD_GELU_F16: return narrow ? VIPT_ERR_ARG : launch2_t<EPI_LNFOLD_GELU_F16, 256, 0>(op, num_sms, st);
   }
   return VIPT_ERR_ARG;
 }
@@ -574,7 +657,7 @@ int gemm2_launch(const GemmOp& op, int num_sms, cudaStream_t st) {
 // same operand conventions as gemm_plan, single group, N % 256 == 0; W box = 128 rows (half tile per CTA)
 int gemm2_plan(GemmOp* op, const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, int epi,
                void* out, int64_t ldc, const float* bias, int num_clusters) {
-  if (K % g2::BK != 0 || N % 128 != 0 || M <= 0 || epi == EPI_RESID_F32 || epi == EPI_RESID_STAT) return VIPT_ERR_ARG;
+  if (K % g2::BK != 0 || N % 128 != 0 || M <= 0 || epi == EPI_RESID_F32 || g2::epi_resid(epi)) return VIPT_ERR_ARG;
   if ((epi == EPI_LNFOLD_F16 || epi == EPI_LNFOLD_GELU_F16) && N % 256 != 0) return VIPT_ERR_ARG;
   // 128-wide pair tiles only when N is not a multiple of 256 (or forced, num_clusters < 0).  Choosing them for the
   // N = 768 layers to shorten the last wave (480 half-tiles = 3.5 rounds instead of 4) was measured and lost:
@@ -602,6 +685,8 @@ int gemm2_plan(GemmOp* op, const void* A, int64_t lda, const void* W, int64_t ld
   if (r) return r;
   op->tmC2 = op->tmC;
   op->tmB2 = op->tmB;
+  op->tmAx = op->tmA;
+  op->tmBx = op->tmB;
   // Tail of the persistent loop: T tiles over C clusters leave the last round partly empty (N = 768 at 64 x 320 rows:
   // 240 tiles = 3.24 rounds of 74, run as 4).  The tiles of that round are cut into 2 or 4 column strips when the strips
   // still fit ONE round; a strip costs more than its share of a tile (the A operand stream does not shrink: measured
@@ -627,6 +712,7 @@ int gemm2_plan(GemmOp* op, const void* A, int64_t lda, const void* W, int64_t ld
   op->p.bias = bias; op->p.resid = nullptr;
   op->p.conv_cb_per_tap = 0; op->p.conv_cin_stride = 0;
   op->p.stat_out = nullptr; op->p.stat_in = nullptr; op->p.stat_parts = 0; op->p.colsum = nullptr; op->p.ln_eps = 0.f;
+  op->p.colw = nullptr; op->p.part_out = nullptr; op->p.kext = 0;
   op->bn = bn == 256 ? 512 : 640;      // marks a 2-CTA plan (256- / 128-wide pair tiles)
   op->epi = epi;
   return VIPT_OK;
@@ -646,6 +732,38 @@ int gemm2_plan_resid_stat(GemmOp* op, const void* A, int64_t lda, const void* W,
   if (r) return r;
   op->p.stat_out = stat_out;
   op->epi = EPI_RESID_STAT;
+  return VIPT_OK;
+}
+
+int gemm2_plan_resid_prompt(GemmOp* op, const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, float* x,
+                            void* x16, const float* bias, const float* colw20, float* part_out) {
+  if (!colw20 || !part_out || (reinterpret_cast<uintptr_t>(colw20) & 15) || (reinterpret_cast<uintptr_t>(part_out) & 15))
+    return VIPT_ERR_ARG;
+  // whole tiles only: the 20 sums of a row are kept per (tile, column half)
+  int r = gemm2_plan_resid_stat(op, A, lda, W, ldw, M, N, K, x, x16, bias, reinterpret_cast<float2*>(part_out), 0);
+  if (r) return r;
+  op->p.stat_out = nullptr;
+  op->p.colw = colw20;
+  op->p.part_out = part_out;
+  op->epi = EPI_RESID_PROMPT;
+  return VIPT_OK;
+}
+
+int gemm2_set_kext(GemmOp* op, const void* Ax, const void* Wx) {
+  if (op->bn != 512 || !Ax || !Wx || (reinterpret_cast<uintptr_t>(Ax) & 15) || (reinterpret_cast<uintptr_t>(Wx) & 15) ||
+      op->p.conv_cb_per_tap)
+    return VIPT_ERR_ARG;
+  uint64_t da[3] = {64, (uint64_t)op->p.M, 1};
+  uint64_t sa[2] = {128, (uint64_t)op->p.M * 128};
+  uint32_t ba[3] = {g2::BK, g2::BM, 1};
+  int r = make_tmap_f16(&op->tmAx, Ax, 3, da, sa, ba);
+  if (r) return r;
+  uint64_t db[3] = {64, (uint64_t)op->p.N, 1};
+  uint64_t sb[2] = {128, (uint64_t)op->p.N * 128};
+  uint32_t bb[3] = {g2::BK, 128, 1};
+  r = make_tmap_f16(&op->tmBx, Wx, 3, db, sb, bb);
+  if (r) return r;
+  op->p.kext = 1;
   return VIPT_OK;
 }
 

@@ -26,6 +26,10 @@ int launch_prompt_b(const float* F, const float* w1, const float* b1, float* P, 
 int launch_prompt_coop(float* x, const void* delta, int n_cur, const int* gi, float* F, float* X0, const float* wg_a,
                        const float* fold, const float* w1t, const float* b1, const float* gamma1, const float* beta1,
                        void* xn, int B, int lens_t, int lens_full, int num_sms, cudaStream_t st);
+// prompt fold (prompt_mid.cu): part (6, B * n_cur, 20) row sums from the fc2 epilogue -> F (raster, in place), f16 (token rows,
+// fp16, 64 columns of which 8 are written), rowstat (token rows) float2 (rstd, -mean * rstd) of norm1's input
+int launch_prompt_mid(const float* part, int n_cur, const int* gi, float* F, const float* fold, const float* fold2, void* f16,
+                      void* rowstat, int B, int lens_t, int lens_full, cudaStream_t st);
 int launch_ce_topk(const float* ce_prob, int n_heads, int n_s, int n_keep, const int* gi_in, int* gi_out, int* perm,
                    int* removed, int* slot_of_pos, float* score_out, int lens_x, int B, cudaStream_t st);
 int launch_final_norm(const float* x, const void* delta, int n_cur, const int* slot_of_pos, const float* gamma, const float* beta,
