@@ -133,9 +133,10 @@ void Engine::plan_schedule() {
     auto pair = [&](int n) { return ((B * n + 255) / 256) * 3 >= num_sms / 2; };
     L[i].fuse_ln2 = opt_lnfold && !ce_keep[i] && pair(n_tok[i]);
     L[i].fuse_ln1 = opt_lnfold && !deep && i >= 1 && pair(n_tok[i]);
-    // prompt fold: the deep-prompt stage of layer i inside the epilogues of fc2[i-1], qkv[i] and proj[i]; proj must be
-    // the residual kind, so not in the candidate-elimination layers (they keep prompt_coop_kernel)
-    PW[i].fold_on = opt_promptfold && deep && i >= 1 && L[i].fuse_ln2;
+    // prompt fold: the deep-prompt stage of layer i inside fc2[i-1], qkv[i] and proj[i] (proj is then the residual kind,
+    // also in the candidate-elimination layers, where the gather + norm2 pass follows it)
+    static const bool no_ce = getenv("VIPT_PROMPT_FOLD_NO_CE") != nullptr;      // measurement switch: keep prompt_coop_kernel in blocks 3 / 6 / 9
+    PW[i].fold_on = opt_promptfold && opt_lnfold && deep && i >= 1 && pair(n_tok[i]) && !(no_ce && ce_keep[i]);
   }
 }
 

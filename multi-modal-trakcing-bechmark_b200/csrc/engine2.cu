@@ -123,14 +123,17 @@ int Engine::finalize_buffers() {
     RET(attention_plan(&a_op[i], qkv, B, n_tok[i]));
     // otherwise proj / fc2 write their branch output as fp16 (dbuf); the residual add is fused into the next
     // LayerNorm / prompt kernel, where it is coalesced
-    if (L[i].fuse_ln2) {
+    if (L[i].fuse_ln2 || PW[i].fold_on) {
       RET(gemm2_plan_resid_stat(&g_proj[i], att, 768, L[i].w_proj, 768, Ma, 768, 768, x_cur, xn,
                                 PW[i].fold_on ? PW[i].b_proj_r8 : L[i].b_proj, lnstat, num_sms / 2));
       if (PW[i].fold_on) RET(gemm2_set_kext(&g_proj[i], F16, PW[i].wx_proj));    // x <- v + U f + b1 + proj(..)
+    } else {
+      RET(plan_lin(&g_proj[i], att, 768, L[i].w_proj, Ma, 768, 768, EPI_BIAS_F16, dbuf, L[i].b_proj));
+    }
+    if (L[i].fuse_ln2) {
       RET(gemm2_plan(&g_fc1[i], xn, 768, L[i].w_fc1, 768, Mm, 3072, 768, EPI_LNFOLD_GELU_F16, hbuf, 3072, L[i].b_fc1, num_sms / 2));
       gemm2_set_lnfold(&g_fc1[i], lnstat, 24, L[i].cs_fc1, 1e-6f);
     } else {
-      RET(plan_lin(&g_proj[i], att, 768, L[i].w_proj, Ma, 768, 768, EPI_BIAS_F16, dbuf, L[i].b_proj));
       RET(plan_lin(&g_fc1[i], xn, 768, L[i].w_fc1, Mm, 3072, 768, EPI_GELU_F16, hbuf, L[i].b_fc1));
     }
     if (ce_keep[i]) { float* t = x_cur; x_cur = x_oth; x_oth = t; }
@@ -231,7 +234,8 @@ int Engine::run_backbone_head(bool tracking, bool want_feat32, int debug_stop, c
     if (ce_keep[i]) {
       LAUNCH(K_NORM, launch_ce_topk(ce_prob, kHeads, n - kLensT, ce_keep[i], gi, gi_other, perm, removed + (size_t)ce_idx * RH,
                          slot_of_pos, ce_score + (size_t)ce_idx * RH, kLensX, B, st));
-      LAUNCH(K_NORM, launch_ln_rows(x, n, dbuf, perm, kLensX, x_other, xn, L[i].ln2_g, L[i].ln2_b, B, nm, kLensT, st));
+      // (prompt fold: attn.proj has already added its branch and the prompt update to x)
+      LAUNCH(K_NORM, launch_ln_rows(x, n, PW[i].fold_on ? nullptr : dbuf, perm, kLensX, x_other, xn, L[i].ln2_g, L[i].ln2_b, B, nm, kLensT, st));
       float* t = x; x = x_other; x_other = t;
       int* tg = gi; gi = gi_other; gi_other = tg == ident ? giB : tg;      // the identity array is never a destination
       ++ce_idx;

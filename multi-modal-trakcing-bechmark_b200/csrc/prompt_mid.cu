@@ -40,6 +40,7 @@ prompt_mid_kernel(const float* __restrict__ part, int M, int n_cur, const int* _
   __shared__ float s_fold[kFoldFloats], s_fold2[kFold2Floats];
   __shared__ float s_red[2][kWarps * 8 * 2];
   __shared__ float s_ms[32];                     // [domain][channel][max, 1 / sum]
+  __shared__ float4 s_sum[320 * 5];              // the 20 sums of every row of the sequence
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int b = blockIdx.x;
   for (int i = tid; i < kFoldFloats; i += kThreads) s_fold[i] = fold[i];
@@ -52,6 +53,37 @@ prompt_mid_kernel(const float* __restrict__ part, int M, int n_cur, const int* _
   const int k = tid & 7, slot = tid >> 3;        // channel, row slot (64 per pass, 5 passes cover 320 rows)
   const size_t row_base = (size_t)b * n_cur;
 
+  // The 6 partial sums of every row are added (fixed order) into shared memory first, one thread per (row, float4): 6
+  // independent 16-byte loads each.  (Read per (row, channel) thread, 150 dependent scalar loads put the kernel at 18 us.)
+  {
+    const float4* p4 = reinterpret_cast<const float4*>(part);
+    for (int idx = tid; idx < n_cur * 5; idx += kThreads) {
+      const int r = idx / 5, j = idx - r * 5;
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      float4 t[kParts];
+#pragma unroll
+      for (int q = 0; q < kParts; ++q) t[q] = __ldcg(p4 + ((size_t)q * M + row_base + r) * 5 + j);
+#pragma unroll
+      for (int q = 0; q < kParts; ++q) { acc.x += t[q].x; acc.y += t[q].y; acc.z += t[q].z; acc.w += t[q].w; }
+      s_sum[r * 5 + j] = acc;
+    }
+  }
+  __syncthreads();
+  // raster position and previous Fovea output of this thread's rows: in flight during the softmax statistics
+  int posv[5];
+  float4 fp0[5], fp1[5];
+#pragma unroll
+  for (int i = 0; i < 5; ++i) {
+    const int r = slot + i * (kThreads / 8);
+    posv[i] = 0;
+    fp0[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    fp1[i] = fp0[i];
+    if (r < n_cur) {
+      posv[i] = r < lens_t ? r : lens_t + gi[b * lens_x + (r - lens_t)];
+      fp0[i] = *reinterpret_cast<const float4*>(F + ((size_t)b * lens_full + posv[i]) * 8);
+      fp1[i] = *reinterpret_cast<const float4*>(F + ((size_t)b * lens_full + posv[i]) * 8 + 4);
+    }
+  }
   float x0[5], sv[5], sq[5], dk[5], ev[5];
   float m[2] = {-INFINITY, -INFINITY};
 #pragma unroll
@@ -59,16 +91,12 @@ prompt_mid_kernel(const float* __restrict__ part, int M, int n_cur, const int* _
     const int r = slot + i * (kThreads / 8);
     x0[i] = 0.f; sv[i] = 0.f; sq[i] = 0.f; dk[i] = 0.f; ev[i] = 0.f;
     if (r < n_cur) {
-      float a = 0.f;
-#pragma unroll
-      for (int q = 0; q < kParts; ++q) {         // fixed order
-        const float* pr = part + ((size_t)q * M + row_base + r) * kPartFloats;
-        sv[i] += __ldcg(pr);
-        sq[i] += __ldcg(pr + 1);
-        a += __ldcg(pr + 2 + k);
-        dk[i] += __ldcg(pr + 10 + k);
-        ev[i] += __ldcg(pr + 18);
-      }
+      const float* pr = reinterpret_cast<const float*>(s_sum + r * 5);
+      sv[i] = pr[0];
+      sq[i] = pr[1];
+      const float a = pr[2 + k];
+      dk[i] = pr[10 + k];
+      ev[i] = pr[18];
       const float mean = sv[i] * (1.0f / 768.0f);
       const float rstd = rsqrtf(fmaxf(fmaf(-mean, mean, sq[i] * (1.0f / 768.0f)), 0.f) + kLnEps);
       x0[i] = fmaf(rstd, fmaf(-mean, s_fold2[kSwa + k], a), s_fold[kCA + k]);
@@ -126,10 +154,9 @@ prompt_mid_kernel(const float* __restrict__ part, int M, int n_cur, const int* _
     float fk = 0.f;
     int pos = 0;
     if (live) {
-      pos = r < lens_t ? r : lens_t + gi[b * lens_x + (r - lens_t)];
+      pos = posv[i];
       const int dom = r < lens_t ? 0 : 1;
-      const float4 f0 = *reinterpret_cast<const float4*>(F + ((size_t)b * lens_full + pos) * 8);
-      const float4 f1 = *reinterpret_cast<const float4*>(F + ((size_t)b * lens_full + pos) * 8 + 4);
+      const float4 f0 = fp0[i], f1 = fp1[i];
       const float f[8] = {f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, f1.z, f1.w};
       float var = s_fold[kC0], a = s_fold[kA0 + k];
 #pragma unroll
@@ -183,7 +210,7 @@ prompt_mid_kernel(const float* __restrict__ part, int M, int n_cur, const int* _
 int launch_prompt_mid(const float* part, int n_cur, const int* gi, float* F, const float* fold, const float* fold2, void* f16,
                       void* rowstat, int B, int lens_t, int lens_full, cudaStream_t st) {
   if (!part || !gi || !F || !fold || !fold2 || !f16 || !rowstat || n_cur < lens_t || n_cur > lens_full ||
-      lens_full > 5 * (pm::kThreads / 8))
+      lens_full > 5 * (pm::kThreads / 8) || lens_full > 320)
     return VIPT_ERR_ARG;
   return launch_pdl(prompt_mid_kernel, dim3(B), dim3(pm::kThreads), 0, st, part, B * n_cur, n_cur, gi, F, fold, fold2,
                     reinterpret_cast<__half*>(f16), reinterpret_cast<float2*>(rowstat), lens_t, lens_full) == cudaSuccess
