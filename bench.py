@@ -191,6 +191,27 @@ def run_ours(args):
             a = prof.setdefault(name, [0.0, 0])
             a[0] += t / nprof; a[1] = n
 
+    fold_info = {"lnfold_layers": eng.info("lnfold_layers"), "promptfold_layers": eng.info("promptfold_layers")}
+    # ================= the same profile with the LayerNorm / prompt folds off (VIPT_NO_LNFOLD, read at engine creation):
+    # the GEMM launches then carry GEMM work only, which is what a tensor-pipe fraction should be quoted on
+    prof_plain = None
+    if world == 1 and (fold_info["lnfold_layers"] or fold_info["promptfold_layers"]) and not args.no_sustained:
+        os.environ["VIPT_NO_LNFOLD"] = "1"
+        try:
+            trk2 = BatchedViPTTracker(sd, B, PROMPT, use_graph=False)
+            trk2.initialize(devf[0], boxes0)
+            trk2.engine.track_enqueue(ptrs[1], False)
+            trk2.engine.results()
+            prof_plain = {}
+            for k in range(nprof):
+                p2 = trk2.engine.profile_step(ptrs[1 + k % RING])
+                for name, (t, n) in p2.items():
+                    a = prof_plain.setdefault(name, [0.0, 0])
+                    a[0] += t / nprof; a[1] = n
+            del trk2
+        finally:
+            del os.environ["VIPT_NO_LNFOLD"]
+
     # ================= e2e: public tracker API, HOST frames, H2D + D2H every step
     # (a) synchronous: track(frames) returns the boxes of this frame before the next call (the reference's call shape)
     trk.initialize(host[0], boxes0)
@@ -297,7 +318,7 @@ def run_ours(args):
                      "whole_step_frac": step_tf / step_peak,
                      "whole_step_frac_burst": step_tf / peak_burst, "whole_step_frac_sustained": step_tf / peak_sust,
                      "whole_step_peak": "sustained (timed region >= 2 s under sw_power_cap)" if step_capped else "burst"},
-        "roofline_hbm": hbm_rooflines(prof, B, final_boxes, peaks, peak_src),
+        "roofline_hbm": hbm_rooflines(prof, B, final_boxes, peaks, peak_src, fold_info),
         "backbone": {"algorithmic_gflop_per_frame": GF_BACKBONE, "ms_per_step": round(bb_ms, 4), "tflops": bb_tf,
                      "frac_of_peak": bb_tf / peak_burst, "frac_burst": bb_tf / peak_burst, "frac_sustained": bb_tf / peak_sust,
                      "what": "patch embed + 12 blocks (linears, attention, prompt blocks, LayerNorms, CE), per-launch CUDA "
@@ -305,6 +326,20 @@ def run_ours(args):
         "kernel_ms_per_step": {k: round(v[0], 4) for k, v in prof.items()},
         "kernel_share": {k: round(v[0] / step_ms_prof, 4) for k, v in prof.items()},
     }
+    # fused launches: the linear-layer GEMMs of the timed region also carry the LayerNorms and the deep-prompt stage
+    # (csrc/gemm2.cu "LayerNorm fold" / "prompt fold"), i.e. HBM-bound work that used to be separate kernels.  Their
+    # roofline is max(flops / tensor peak, bytes / HBM peak) per launch, summed over the launches of a step.
+    out["roofline"]["fold"] = dict(fold_info, **fused_bound(B, prof["gemm_linear"][0], peak_burst, float(peaks.get("hbm_gbs", 6650.0)),
+                                                            fold_info))
+    if prof_plain:
+        g_ms = prof_plain["gemm_linear"][0] + prof_plain["gemm_head"][0]
+        tf = gemm_flops / (g_ms * 1e-3) / 1e12
+        out["roofline"]["plain_gemm"] = {
+            "achieved": tf, "frac_burst": tf / peak_burst, "frac_sustained": tf / peak_sust, "ms_per_step": round(g_ms, 4),
+            "launches_per_step": prof_plain["gemm_linear"][1] + prof_plain["gemm_head"][1],
+            "kernel_ms_per_step": {k: round(v[0], 4) for k, v in prof_plain.items()},
+            "what": "the same engine with VIPT_NO_LNFOLD=1 (LayerNorms and prompt blocks as separate kernels): the GEMM "
+                    "launches carry GEMM work only; same per-launch CUDA-event method"}
     out["sustained"] = sustained
     if world == 1:
         out["latency_bs1"] = latency_bs1(sd, seqs[0], dev)
@@ -322,7 +357,32 @@ _N_TOK = [320, 320, 320, 320, 244, 244, 244, 190, 190, 190, 153, 153]      # tok
 _N_MLP = [320, 320, 320, 244, 244, 244, 190, 190, 190, 153, 153, 153]      # tokens after block i's CE
 
 
-def hbm_rooflines(prof, B, boxes, peaks, peak_src):
+def fused_bound(B, gemm_linear_ms, peak_tf, hbm_gbs, fold):
+    """Lower bound of the linear-layer GEMM launches of one step: sum over launches of max(flops / tensor peak,
+    algorithmic bytes / HBM peak).  Bytes: fp16 A and W read, output written; a residual epilogue (attn.proj, and mlp.fc2
+    before a folded prompt stage) also reads and writes the fp32 rows and writes their fp16 copy (10 B per element)."""
+    pf, lf = fold["promptfold_layers"] > 0, fold["lnfold_layers"] > 0
+    t = 0.0
+    byts = 0.0
+    for i in range(12):
+        ma, mm = B * _N_TOK[i], B * _N_MLP[i]
+        ce = i in (3, 6, 9)
+        proj_resid = (lf and not ce) or (pf and i >= 1)
+        fc2_resid = pf and i + 1 < 12
+        for (m, n, k, resid) in ((ma, 2304, 768, False), (ma, 768, 768, proj_resid), (mm, 3072, 768, False), (mm, 768, 3072, fc2_resid)):
+            fl = 2.0 * m * n * k
+            by = 2.0 * (m * k + n * k) + (10.0 if resid else 2.0) * m * n
+            t += max(fl / (peak_tf * 1e12), by / (hbm_gbs * 1e9))
+            byts += by
+    t += 2 * max(2.0 * B * 320 * 768 * 768 / (peak_tf * 1e12), (B * 320 * 768 * (2 + 4) + 768 * 768 * 2) / (hbm_gbs * 1e9))   # patch embed x 2
+    return {"bound_ms_per_step": t * 1e3, "measured_ms_per_step": round(gemm_linear_ms, 4),
+            "frac_of_fused_bound": t * 1e3 / gemm_linear_ms if gemm_linear_ms > 0 else None,
+            "algorithmic_bytes_per_step": byts,
+            "what": "linear-layer GEMM launches incl. their fused LayerNorm / prompt work against "
+                    "sum over launches of max(flops / burst tensor peak, bytes / measured HBM peak)"}
+
+
+def hbm_rooflines(prof, B, boxes, peaks, peak_src, fold=None):
     """Achieved HBM GB/s of the memory-bound kernel classes: ALGORITHMIC bytes of one step (every operand read or
     written once at the data types the engine uses: fp32 residual stream, fp16 branch outputs / GEMM operands, u8
     frames) divided by the class's summed launch durations (CUDA-event pairs, un-graphed step).  Part of the fp32
@@ -331,6 +391,14 @@ def hbm_rooflines(prof, B, boxes, peaks, peak_src):
     row = 768 * (4 + 2 + 4 + 2)                              # read x fp32 + branch fp16, write x fp32 + xn fp16
     prompt = sum(_N_TOK[1:]) * row + 320 * 768 * (4 + 4 + 4 + 2)      # layers 1..11; layer 0: E_rgb, E_x -> x, xn
     norm = sum(_N_MLP) * row + 153 * 768 * (4 + 2) + 256 * 768 * 2     # 12 x LN2 (+ CE gather), final norm + recover
+    if fold and fold.get("promptfold_layers", 0) == 11:
+        # prompt fold: layers 1..11 are prompt_mid_kernel (per row: 6 x 80 B of sums, Fovea in / out, 9 fp16, statistics)
+        prompt = sum(_N_TOK[1:]) * (6 * 80 + 32 + 32 + 18 + 8) + 320 * 768 * (4 + 4 + 4 + 2)
+    if fold and fold.get("lnfold_layers", 0) > 0:
+        # LayerNorm fold: only the 3 gather + norm2 passes of the CE blocks (x read, x and xn written; + the branch output
+        # when attn.proj is not the residual kind) and the final norm are left
+        ce_row = 768 * (4 + 4 + 2) + (0 if fold.get("promptfold_layers", 0) == 11 else 768 * 2)
+        norm = sum(_N_MLP[i] for i in (3, 6, 9)) * ce_row + 153 * 768 * (4 + 2) + 256 * 768 * 2
     cs = np.ceil(np.sqrt(np.maximum(boxes[:, 2] * boxes[:, 3], 0.0)) * 4.0)
     crop = float(np.mean(np.minimum(cs, 630) * np.minimum(cs, 480) * 6)) + 6 * 256 * 256 * 2     # clipped rectangle + patch rows
     out = {"peak": hbm, "unit": "GB/s", "peak_source": "%s hbm_gbs (copy bandwidth)" % peak_src, "kernels": {}}

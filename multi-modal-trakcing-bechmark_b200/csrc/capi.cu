@@ -120,6 +120,7 @@ int vipt_engine_create(void** out) {
   e->opt_speculate = getenv("VIPT_NO_SPECULATION") == nullptr;
   e->opt_lnfold = getenv("VIPT_NO_LNFOLD") == nullptr;
   e->opt_promptfold = getenv("VIPT_NO_PROMPT_FOLD") == nullptr;
+  e->opt_promptfold_ce = getenv("VIPT_PROMPT_FOLD_NO_CE") == nullptr;
   *out = e;
   return VIPT_OK;
 }

@@ -135,8 +135,7 @@ void Engine::plan_schedule() {
     L[i].fuse_ln1 = opt_lnfold && !deep && i >= 1 && pair(n_tok[i]);
     // prompt fold: the deep-prompt stage of layer i inside fc2[i-1], qkv[i] and proj[i] (proj is then the residual kind,
     // also in the candidate-elimination layers, where the gather + norm2 pass follows it)
-    static const bool no_ce = getenv("VIPT_PROMPT_FOLD_NO_CE") != nullptr;      // measurement switch: keep prompt_coop_kernel in blocks 3 / 6 / 9
-    PW[i].fold_on = opt_promptfold && opt_lnfold && deep && i >= 1 && pair(n_tok[i]) && !(no_ce && ce_keep[i]);
+    PW[i].fold_on = opt_promptfold && opt_lnfold && deep && i >= 1 && pair(n_tok[i]) && (opt_promptfold_ce || !ce_keep[i]);
   }
 }
 

@@ -108,6 +108,7 @@ struct Engine {
   bool opt_lnfold = true;
   // VIPT_NO_PROMPT_FOLD=1 keeps the deep-prompt stage in prompt_coop_kernel at every layer; same rules
   bool opt_promptfold = true;
+  bool opt_promptfold_ce = true;           // VIPT_PROMPT_FOLD_NO_CE=1: blocks 3 / 6 / 9 keep prompt_coop_kernel (measurement switch)
   void plan_schedule();                    // CE schedule + which LayerNorms are folded (needs B, deep, num_sms)
   // zero-copy gather: the device-visible addresses of the B host frames travel as a kernel parameter
   static constexpr int kRoiSlots = 4;      // steps that may be enqueued before their results are collected

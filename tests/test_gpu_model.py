@@ -143,3 +143,31 @@ def test_outlier_channels_fp16_range():
     # of the maximum (3e-3 .. 7.5e-3 over the four samples).  The stress case therefore gets 2e-2, the regular weight
     # sets keep the north-star 1e-2.
     _check_model(m, out, z, x, "vipt_deep", "outlier", tol_map=2e-2)
+
+
+@pytest.mark.parametrize("switch,want", [("VIPT_NO_LNFOLD", (0, 0)), ("VIPT_NO_PROMPT_FOLD", (9, 0)), ("VIPT_PROMPT_FOLD_NO_CE", (9, 8))])
+def test_fold_switches(monkeypatch, switch, want):
+    """LayerNorm fold / prompt fold (csrc/gemm2.cu, prompt_mid.cu) against the same engine with the fold switched off
+    (environment read once at engine creation): the states both forms materialise before the first candidate
+    elimination -- qkv of block 1, the residual stream after attn.proj + norm2 of block 2, fc1's output of block 2 --
+    agree to fp16-operand accuracy at the large-batch size where the folds are active."""
+    from vipt_b200.engine import NativeEngine
+    B = 64
+    sd = synth.weight_set("peaked", "vipt_deep")
+    g = torch.Generator().manual_seed(11)
+    z = torch.randn(B, 6, 128, 128, generator=g).cuda()
+    x = torch.randn(B, 6, 256, 256, generator=g).cuda()
+    on = NativeEngine(sd, B, "vipt_deep")
+    assert (on.info("lnfold_layers"), on.info("promptfold_layers")) == (9, 11)
+    monkeypatch.setenv(switch, "1")
+    off = NativeEngine(sd, B, "vipt_deep")
+    monkeypatch.delenv(switch)
+    assert (off.info("lnfold_layers"), off.info("promptfold_layers")) == want
+    width = {"qkv": 2304, "hbuf": 3072, "xA": 768}
+    for stage, name in ((4 + 7, "qkv"), (7 + 14, "xA"), (8 + 14, "hbuf")):
+        on.forward(z, x, debug_stop=stage)
+        off.forward(z, x, debug_stop=stage)
+        n = B * 320 * width[name]
+        a, b = on.buffer(name).flatten()[:n].float(), off.buffer(name).flatten()[:n].float()
+        rel = ((a - b).abs().max() / b.abs().max()).item()
+        assert rel < 5e-3, (switch, name, rel)
