@@ -40,10 +40,18 @@ int vipt_op_gemm_resid_stat(const void* A, int64_t lda, const void* W, int64_t l
                             const float* bias, float* stat_out, void* stream);
 /* Consumer: out fp16 = [gelu](rstd * (A W^T - mean * colsum) + bias) with mean / rstd of every row of A (width K) from
  * stat_in (stat_parts, M, 2); the caller passes W = fp16(gamma * W0), colsum = row sums of that fp16 W and
- * bias = b0 + W0 beta, which makes this LayerNorm(x) W0^T + b0. */
+ * bias = b0 + W0 beta, which makes this LayerNorm(x) W0^T + b0.  stat_parts = 0: stat_in (M, 2) holds the final
+ * (rstd, -mean * rstd) of every row.  Ax (M, 64) / Wx (N, 64) fp16 or both NULL: one extra k-block, acc += Ax Wx^T (the
+ * rank-8 prompt update of ViPT/lib/models/vipt/vit_ce_prompt.py:308-310 on the tensor pipe). */
 int vipt_op_gemm_lnfold(const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, int gelu, void* out,
                         int64_t ldc, const float* bias, const float* colsum, const float* stat_in, int stat_parts, float eps,
-                        void* stream);
+                        const void* Ax, const void* Wx, void* stream);
+/* Prompt fold, producer (mlp.fc2 before a deep-prompt stage, vit_ce_prompt.py:268-310): x <- x + A W^T + bias in place,
+ * x16 = fp16(x), and part_out (2*N/256, M, 20) fp32: per row and (256-column tile t, half h: the 16-column groups h, h+2, ..
+ * of the tile) the sums {x, x^2, x.wa_0..7, x.u_0..7, x.b1, 0} over the part's columns; colw20 (N, 20) fp32 holds
+ * wa_0..7, u_0..7, b1, 3 pad per column. */
+int vipt_op_gemm_resid_prompt(const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, float* x, void* x16,
+                              const float* bias, const float* colw20, float* part_out, void* stream);
 
 /* Fused crop + zero pad + cv2-exact bilinear resize + /255, mean, std + patch-major store.  Replaces
  * sample_target (ViPT/lib/train/data/processing_utils.py:14-76) + PreprocessorMM.process

@@ -23,7 +23,9 @@ SIGNATURES = {
     "vipt_op_gemm_resid_stat": (c_int, [c_void_p, c_i64, c_void_p, c_i64, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                         c_void_p, c_void_p]),
     "vipt_op_gemm_lnfold": (c_int, [c_void_p, c_i64, c_void_p, c_i64, c_int, c_int, c_int, c_int, c_void_p, c_i64, c_void_p,
-                                    c_void_p, c_void_p, c_int, c_float, c_void_p]),
+                                    c_void_p, c_void_p, c_int, c_float, c_void_p, c_void_p, c_void_p]),
+    "vipt_op_gemm_resid_prompt": (c_int, [c_void_p, c_i64, c_void_p, c_i64, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                                          c_void_p, c_void_p, c_void_p]),
     "vipt_op_crop": (c_int, [c_void_p, c_void_p, c_void_p, c_double, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                              c_int, c_void_p]),
     "vipt_op_attention": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p]),

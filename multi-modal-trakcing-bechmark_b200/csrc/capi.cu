@@ -43,15 +43,25 @@ int vipt_op_gemm_resid_stat(const void* A, int64_t lda, const void* W, int64_t l
   if (r) set_err(cudaGetErrorString(cudaGetLastError()));
   return r;
 }
+int vipt_op_gemm_resid_prompt(const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, float* x, void* x16,
+                              const float* bias, const float* colw20, float* part_out, void* stream) {
+  vipt::GemmOp op;
+  int r = vipt::gemm2_plan_resid_prompt(&op, A, lda, W, ldw, M, N, K, x, x16, bias, colw20, part_out);
+  if (r) { set_err("gemm2_plan_resid_prompt failed"); return r; }
+  r = vipt::gemm_launch(op, num_sms(), (cudaStream_t)stream);
+  if (r) set_err(cudaGetErrorString(cudaGetLastError()));
+  return r;
+}
 int vipt_op_gemm_lnfold(const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, int gelu, void* out,
                         int64_t ldc, const float* bias, const float* colsum, const float* stat_in, int stat_parts, float eps,
-                        void* stream) {
-  if (!colsum || !stat_in || stat_parts < 1) return VIPT_ERR_ARG;
+                        const void* Ax, const void* Wx, void* stream) {
+  if (!colsum || !stat_in || stat_parts < 0 || (Ax == nullptr) != (Wx == nullptr)) return VIPT_ERR_ARG;
   vipt::GemmOp op;
   int r = vipt::gemm2_plan(&op, A, lda, W, ldw, M, N, K, gelu ? vipt::EPI_LNFOLD_GELU_F16 : vipt::EPI_LNFOLD_F16, out, ldc, bias,
                              num_sms() / 2);
   if (r) { set_err("gemm2_plan (LayerNorm fold) failed"); return r; }
   vipt::gemm2_set_lnfold(&op, (const float2*)stat_in, stat_parts, colsum, eps);
+  if (Ax && (r = vipt::gemm2_set_kext(&op, Ax, Wx))) { set_err("gemm2_set_kext failed"); return r; }
   r = vipt::gemm_launch(op, num_sms(), (cudaStream_t)stream);
   if (r) set_err(cudaGetErrorString(cudaGetLastError()));
   return r;

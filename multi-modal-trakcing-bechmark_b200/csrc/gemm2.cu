@@ -40,6 +40,10 @@
 
 namespace vipt {
 
+#ifndef G2_ABL        // timing experiments only (scripts/ablate_gemm2.sh): 1 no output stores, 2 no prompt sums, 4 no x slab loads
+#define G2_ABL 0
+#endif
+
 namespace g2 {
 constexpr int BM = 128;            // rows per CTA (256 per pair)
 constexpr int BK = 64;
@@ -349,8 +353,8 @@ gemm2_kernel(const __grid_constant__ Gemm2Maps tm, GemmParams p) {
       for (int j = 0; j < un.width / 32; ++j) {
         mbar_wait(&rempty_bar[rs], rph ^ 1);
         if (elect_one()) {
-          mbar_expect_tx(&rfull_bar[rs], kSlabBytes + (kPrompt ? kColwStep : 0));
-          tma_load_3d(slab + rs * kInBytes, &tm.C, &rfull_bar[rs], n0 + j * 32, row0, 0);
+          mbar_expect_tx(&rfull_bar[rs], ((G2_ABL & 4) ? 0 : kSlabBytes) + (kPrompt ? kColwStep : 0));
+          if (!(G2_ABL & 4)) tma_load_3d(slab + rs * kInBytes, &tm.C, &rfull_bar[rs], n0 + j * 32, row0, 0);
           if (kPrompt)
             asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                          ::"r"(smem_u32(slab + rs * kInBytes + kSlabBytes)), "l"(p.colw + (size_t)(n0 + j * 32) * 20),
@@ -448,7 +452,7 @@ gemm2_kernel(const __grid_constant__ Gemm2Maps tm, GemmParams p) {
             s1 += f[k];
             s2 = fmaf(f[k], f[k], s2);
           }
-          if (kPrompt) {         // 17 more row sums: packed FMAs on the (wa, u) pairs of the column, broadcast from smem
+          if (kPrompt && !(G2_ABL & 2)) {         // 17 more row sums: packed FMAs on the (wa, u) pairs of the column, broadcast from smem
             const uint32_t wrow = in_base + kSlabBytes + hh * 16 * 80;
 #pragma unroll
             for (int c = 0; c < 16; ++c) {
@@ -492,7 +496,7 @@ gemm2_kernel(const __grid_constant__ Gemm2Maps tm, GemmParams p) {
           // the next step writes
           if (kOut == 2 && et == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
           asm volatile("bar.sync 1, 256;" ::: "memory");
-          if (et == 0) {
+          if (et == 0 && !(G2_ABL & 1)) {
             asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
                          ::"l"(reinterpret_cast<uint64_t>(&tm.C)), "r"(smem_u32(out_slab + ob * kOutBytes)),
                            "r"(n0 + j * 32), "r"(row0), "r"(0)

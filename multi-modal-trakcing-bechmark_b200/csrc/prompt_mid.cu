@@ -151,26 +151,32 @@ prompt_mid_kernel(const float* __restrict__ part, int M, int n_cur, const int* _
   for (int i = 0; i < 5; ++i) {
     const int r = slot + i * (kThreads / 8);
     const bool live = r < n_cur;
-    float fk = 0.f;
+    float fk = 0.f, varp = 0.f, a = 0.f;
     int pos = 0;
     if (live) {
       pos = posv[i];
-      const int dom = r < lens_t ? 0 : 1;
       const float4 f0 = fp0[i], f1 = fp1[i];
       const float f[8] = {f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, f1.z, f1.w};
-      float var = s_fold[kC0], a = s_fold[kA0 + k];
+      // var(f) = f^T G f + 2 h.f + c0 is the same for the 8 channels of a row: lane k contributes f_k (G_k.f + 2 h_k),
+      // the 8 lanes of the row add up below (every lane of the warp takes part in the shuffles)
+      float g = 0.f, g1 = 0.f;
+      a = s_fold[kA0 + k];
 #pragma unroll
-      for (int p = 0; p < 8; ++p) {
-        float g = 0.f, g1 = 0.f;
-#pragma unroll
-        for (int qq = 0; qq < 8; qq += 2) {
-          g += s_fold[kG + p * 8 + qq] * f[qq];
-          g1 += s_fold[kG + p * 8 + qq + 1] * f[qq + 1];
-        }
-        g += g1;
-        var += f[p] * (g + 2.0f * s_fold[kH + p]);
-        a += s_fold[kA + k * 8 + p] * f[p];
+      for (int qq = 0; qq < 8; qq += 2) {
+        g += s_fold[kG + k * 8 + qq] * f[qq];
+        g1 += s_fold[kG + k * 8 + qq + 1] * f[qq + 1];
       }
+      const float4 fh = (k & 4) ? f1 : f0;             // f[k] without a dynamically indexed register array
+      const float fsel = (k & 2) ? ((k & 1) ? fh.w : fh.z) : ((k & 1) ? fh.y : fh.x);
+      varp = fsel * (g + g1 + 2.0f * s_fold[kH + k]);
+#pragma unroll
+      for (int p = 0; p < 8; ++p) a += s_fold[kA + k * 8 + p] * f[p];
+    }
+#pragma unroll
+    for (int o = 1; o <= 4; o <<= 1) varp += __shfl_xor_sync(0xffffffffu, varp, o);
+    if (live) {
+      const int dom = r < lens_t ? 0 : 1;
+      const float var = s_fold[kC0] + varp;
       const float x1 = a * rsqrtf(fmaxf(var, 0.f) + kLnEps) + s_fold[kCD + k];
       fk = expf(x0[i] * smooth - s_ms[(dom * 8 + k) * 2]) * s_ms[(dom * 8 + k) * 2 + 1] * x0[i] + x1;
     }

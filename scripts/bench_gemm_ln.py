@@ -1,5 +1,5 @@
 """Time the LayerNorm-fold GEMM pair against the plain GEMMs (CUDA events, L2 flushed between launches).
-usage: python scripts/bench_gemm_ln.py [B] [only]   (only = resid|fold|plain: a single kernel class, for ncu)"""
+usage: python scripts/bench_gemm_ln.py [B] [only]   (only = resid|fold|plain|prompt: a single kernel class, for ncu)"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
@@ -45,5 +45,10 @@ for n in (320, 244, 190, 153):
     if only in ("", "resid"):
         res["proj_resid_stat"] = timeit(lambda: _lib.check(L.vipt_op_gemm_resid_stat(_lib.ptr(att), 768, _lib.ptr(Wp), 768, M, 768, 768, _lib.ptr(x), _lib.ptr(x16), _lib.ptr(bp), _lib.ptr(stat), sp)))
     if only in ("", "fold"):
-        res["fc1_lnfold"] = timeit(lambda: _lib.check(L.vipt_op_gemm_lnfold(_lib.ptr(x16), 768, _lib.ptr(W1), 768, M, 3072, 768, 1, _lib.ptr(h), 3072, _lib.ptr(b1), _lib.ptr(cs), _lib.ptr(stat), 24, 1e-6, sp)))
+        res["fc1_lnfold"] = timeit(lambda: _lib.check(L.vipt_op_gemm_lnfold(_lib.ptr(x16), 768, _lib.ptr(W1), 768, M, 3072, 768, 1, _lib.ptr(h), 3072, _lib.ptr(b1), _lib.ptr(cs), _lib.ptr(stat), 24, 1e-6, None, None, sp)))
+    if only in ("", "prompt"):
+        colw = torch.randn(768, 20, device="cuda") * 0.1
+        part = torch.empty(6, M, 20, device="cuda")
+        res["fc2_resid_prompt"] = timeit(lambda: _lib.check(L.vipt_op_gemm_resid_prompt(_lib.ptr(h), 3072, _lib.ptr(W2), 3072, M, 768, 3072, _lib.ptr(x), _lib.ptr(x16), _lib.ptr(bp), _lib.ptr(colw), _lib.ptr(part), sp)))
+        res["fc2_resid_stat"] = timeit(lambda: _lib.check(L.vipt_op_gemm_resid_stat(_lib.ptr(h), 3072, _lib.ptr(W2), 3072, M, 768, 3072, _lib.ptr(x), _lib.ptr(x16), _lib.ptr(bp), _lib.ptr(stat), sp)))
     print("B=%d n=%d M=%d  " % (B, n, M) + "  ".join("%s %.1f us" % kv for kv in res.items()), flush=True)
