@@ -16,7 +16,7 @@ fi
 python scripts/one_step.py 64 2 > $out/${tag}_plain.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none --csv \
     --log-file $out/${tag}_launches_b64.csv python scripts/one_step.py 64 2 > $out/${tag}_ncu_launches.log 2>&1
-# full capture of the kernels of block 1 (prompt, qkv, attention, proj, LN, fc1, fc2)
+# full capture of the kernels of block 1: fc2 of block 0 (prompt-fold producer), prompt_mid, qkv, attention, proj, fc1, fc2
 python scripts/one_step.py 64 1 > $out/${tag}_plain1.log 2>&1 && \
-ncu --set full --clock-control none --import-source on -s 16 -c 8 -f -o $out/${tag}_top python scripts/one_step.py 64 1 > $out/${tag}_ncu_full.log 2>&1
+ncu --set full --clock-control none --import-source on -s 11 -c 7 -f -o $out/${tag}_top python scripts/one_step.py 64 1 > $out/${tag}_ncu_full.log 2>&1
 ls -la $out | grep ${tag}
