@@ -50,7 +50,18 @@ constexpr int BK = 64;
 constexpr int kSlabCols = 64;                        // epilogue slab: 128 rows x 64 fp16 = 16 KB, SW128
 constexpr int kSlabBytes = BM * kSlabCols * 2;
 constexpr int kABytes = BM * BK * 2;
-constexpr int kThreads = 384;          // warp 0 TMA, 1 MMA, 2 TMEM alloc, 3 epilogue feeder, 4..11 epilogue (2 per TMEM lane group)
+// warp 0 TMA, 1 MMA, 2 TMEM alloc, 3 epilogue feeder, 4..11 epilogue: 8 warps, 2 per TMEM lane group, 32 columns of a
+// 64-column slab each.  -DG2_EPI16=1 builds the epilogues with real math per element (GELU, LayerNorm fold) with 16
+// warps (4 per lane group, 16 columns each, 96 registers): measured and NOT kept -- fc1 + GELU 70.7 -> 72.7 us, fc1 with
+// the LayerNorm fold 78.8 -> 83.0 us at 64 x 320 rows, step 3.80 -> 3.84 ms on the same box (twice the barrier
+// participants and TMEM load instructions per slab for the same FMA work).
+#ifndef G2_EPI16
+#define G2_EPI16 0
+#endif
+__host__ __device__ constexpr int epi_warps(int epi) {
+  return (G2_EPI16 && (epi == EPI_GELU_F16 || epi == EPI_LNFOLD_GELU_F16 || epi == EPI_LNFOLD_F16)) ? 16 : 8;
+}
+__host__ __device__ constexpr int threads_of(int epi) { return 128 + 32 * epi_warps(epi); }
 constexpr int kRingMax = 3;            // residual epilogues: x slabs in flight towards the epilogue (barrier slots)
 __host__ __device__ constexpr bool epi_resid(int epi) { return epi == EPI_RESID_STAT || epi == EPI_RESID_PROMPT; }
 constexpr int kColwStep = 32 * 20 * 4;     // EPI_RESID_PROMPT: the 20 constants of a step's 32 columns travel with its x slab
@@ -137,12 +148,15 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
       : "memory");
 }
 
+__device__ __forceinline__ void tmem_ldc(uint32_t taddr, uint32_t (&v)[32]) { tmem_ld32(taddr, v); }
+__device__ __forceinline__ void tmem_ldc(uint32_t taddr, uint32_t (&v)[16]) { tmem_ld16(taddr, v); }
+
 struct Gemm2Maps {
   CUtensorMap A, B, C, C2, B2, Ax, Bx;
 };
 
 template <int EPI, int BN, int DEEPK>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(g2::kThreads, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(g2::threads_of(EPI), 1)
 gemm2_kernel(const __grid_constant__ Gemm2Maps tm, GemmParams p) {
   using namespace g2;
   using C = Cfg<BN, EPI, DEEPK>;
@@ -151,6 +165,9 @@ gemm2_kernel(const __grid_constant__ Gemm2Maps tm, GemmParams p) {
   constexpr bool kPrompt = EPI == EPI_RESID_PROMPT;          // residual + the sums of the prompt block
   constexpr bool kFold = EPI == EPI_LNFOLD_F16 || EPI == EPI_LNFOLD_GELU_F16;
   constexpr int kIn = C::kIn, kOut = C::kOut, kInBytes = C::kInBytes, kOutBytes = C::kOutBytes;
+  constexpr int kEpiWarps = epi_warps(EPI), kEpiThreads = 32 * kEpiWarps;
+  constexpr int CW = 64 / (kEpiWarps / 4);                   // columns of a 64-column slab per epilogue thread
+  static_assert(kEpiWarps == 8 || (!kResid && EPI != EPI_BIAS_F32), "16 epilogue warps: fp16-output epilogues only");
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* tiles = smem;
@@ -201,7 +218,7 @@ gemm2_kernel(const __grid_constant__ Gemm2Maps tm, GemmParams p) {
     if (p.kext) { tma_prefetch_desc(&tm.Ax); tma_prefetch_desc(&tm.Bx); }
     for (int s = 0; s < kRingMax; ++s) {
       mbar_init(&rfull_bar[s], 1);
-      mbar_init(&rempty_bar[s], 8);   // 8 epilogue warps
+      mbar_init(&rempty_bar[s], kEpiWarps);
     }
     for (int s = 0; s < kStages; ++s) {
       mbar_init(&full_bar[s], 1);
@@ -209,7 +226,7 @@ gemm2_kernel(const __grid_constant__ Gemm2Maps tm, GemmParams p) {
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tfull_bar[a], 1);
-      mbar_init(&tempty_bar[a], 16);  // 8 epilogue warps x 2 CTAs (leader's copy is the one used)
+      mbar_init(&tempty_bar[a], 2 * kEpiWarps);  // epilogue warps x 2 CTAs (leader's copy is the one used)
     }
     fence_mbar_init();
   }
@@ -367,7 +384,7 @@ gemm2_kernel(const __grid_constant__ Gemm2Maps tm, GemmParams p) {
   } else if (warp >= 4) {
     // ------------------------------------------------ epilogue (both CTAs, own 128 rows)
     const int we = (warp - 4) & 3;           // TMEM lane group (warp % 4)
-    const int hh = (warp - 4) >> 2;          // which 32-column half of every 64-column slab
+    const int hh = (warp - 4) >> 2;          // which CW-column part of every 64-column slab
     const int et = threadIdx.x - 128;
     const uint32_t bias_u32 = smem_u32(bias_s);
     int as = 0;
@@ -415,7 +432,7 @@ gemm2_kernel(const __grid_constant__ Gemm2Maps tm, GemmParams p) {
         __syncwarp();
         if (lane == 0) mbar_arrive(&rempty_bar[slot]);
       }
-      asm volatile("bar.sync 1, 256;" ::: "memory");
+      asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");
       mbar_wait(&tfull_bar[as], aph);
       tc_fence_after();
       if constexpr (kResid) {
@@ -526,21 +543,21 @@ gemm2_kernel(const __grid_constant__ Gemm2Maps tm, GemmParams p) {
         if (++as == 2) { as = 0; aph ^= 1; }
         continue;
       }
-      const uint32_t taddr0 = tmem_base + as * BN + hh * 32 + ((uint32_t)(we * 32) << 16);
-      uint32_t v[32];
-      tmem_ld32(taddr0, v);
+      const uint32_t taddr0 = tmem_base + as * BN + hh * CW + ((uint32_t)(we * 32) << 16);
+      uint32_t v[CW];
+      tmem_ldc(taddr0, v);
 #pragma unroll 1
       for (int sl = 0; sl < n_slabs; ++sl) {
         // fp16 outputs: one 64-column slab per step; fp32 outputs: each warp set fills its own 32-column slab
         uint8_t* buf = slab + (EPI == EPI_BIAS_F32 ? ((sl & 1) * 2 + hh) : (sl & 1)) * kSlabBytes;
         const uint32_t prow = smem_u32(buf) + r * 128;
-        const uint32_t brow = bias_u32 + (sl * kSlabCols + hh * 32) * 4;
-        float f[32];
+        const uint32_t brow = bias_u32 + (sl * kSlabCols + hh * CW) * 4;
+        float f[CW];
         tmem_ld_wait();
         if (kFold) {
-          const uint32_t crow = smem_u32(cs_s) + (sl * kSlabCols + hh * 32) * 4;
+          const uint32_t crow = smem_u32(cs_s) + (sl * kSlabCols + hh * CW) * 4;
 #pragma unroll
-          for (int j = 0; j < 32; j += 4) {
+          for (int j = 0; j < CW; j += 4) {
             const float4 bq = lds128f(brow + j * 4);
             const float4 cq = lds128f(crow + j * 4);
             f[j] = fmaf(ln_rs, __uint_as_float(v[j]), fmaf(ln_nm, cq.x, bq.x));
@@ -550,30 +567,30 @@ gemm2_kernel(const __grid_constant__ Gemm2Maps tm, GemmParams p) {
           }
         } else {
 #pragma unroll
-          for (int j = 0; j < 32; j += 4) {
+          for (int j = 0; j < CW; j += 4) {
             const float4 bq = lds128f(brow + j * 4);
             f[j] = __uint_as_float(v[j]) + bq.x; f[j + 1] = __uint_as_float(v[j + 1]) + bq.y;
             f[j + 2] = __uint_as_float(v[j + 2]) + bq.z; f[j + 3] = __uint_as_float(v[j + 3]) + bq.w;
           }
         }
-        if (sl + 1 < n_slabs) tmem_ld32(taddr0 + (sl + 1) * kSlabCols, v);     // in flight during the math below
+        if (sl + 1 < n_slabs) tmem_ldc(taddr0 + (sl + 1) * kSlabCols, v);     // in flight during the math below
         if (EPI == EPI_GELU_F16 || EPI == EPI_LNFOLD_GELU_F16) {
 #pragma unroll
-          for (int j = 0; j < 32; j += 2) gelu_erf2x2(f[j], f[j + 1]);
+          for (int j = 0; j < CW; j += 2) gelu_erf2x2(f[j], f[j + 1]);
         }
         if (EPI == EPI_RELU_F16) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+          for (int j = 0; j < CW; ++j) f[j] = fmaxf(f[j], 0.f);
         }
         if (EPI == EPI_BIAS_F32) {
 #pragma unroll
-          for (int q = 0; q < 8; ++q)                          // 128-byte rows of 32 fp32, 128-byte swizzle
+          for (int q = 0; q < CW / 4; ++q)                     // 128-byte rows of 32 fp32, 128-byte swizzle
             sts128(prow + ((q ^ (r & 7)) * 16), __float_as_uint(f[q * 4 + 0]), __float_as_uint(f[q * 4 + 1]),
                    __float_as_uint(f[q * 4 + 2]), __float_as_uint(f[q * 4 + 3]));
         } else {
 #pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const int chunk = (hh * 4 + q) ^ (r & 7);          // 128-byte swizzle, matches tmC
+          for (int q = 0; q < CW / 8; ++q) {
+            const int chunk = (hh * (CW / 8) + q) ^ (r & 7);   // 128-byte swizzle, matches tmC
             sts128(prow + chunk * 16, pack_op2(f[q * 8 + 0], f[q * 8 + 1]), pack_op2(f[q * 8 + 2], f[q * 8 + 3]),
                    pack_op2(f[q * 8 + 4], f[q * 8 + 5]), pack_op2(f[q * 8 + 6], f[q * 8 + 7]));
           }
@@ -582,7 +599,7 @@ gemm2_kernel(const __grid_constant__ Gemm2Maps tm, GemmParams p) {
         // one barrier per slab: before it, the issuing thread makes sure the PREVIOUS store has drained its
         // staging buffer, which is the buffer the next slab writes
         if (et == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-        asm volatile("bar.sync 1, 256;" ::: "memory");
+        asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");
         if (et == 0) {
           if (EPI == EPI_BIAS_F32) {
 #pragma unroll
@@ -633,7 +650,7 @@ static int launch2_t(const GemmOp& op, int num_sms, cudaStream_t st) {
   if (grid > cap) grid = cap;
   Gemm2Maps tm;
   tm.A = op.tmA; tm.B = op.tmB; tm.C = op.tmC; tm.C2 = op.tmC2; tm.B2 = op.tmB2; tm.Ax = op.tmAx; tm.Bx = op.tmBx;
-  return launch_pdl(gemm2_kernel<EPI, BN, DEEPK>, grid, g2::kThreads, C::kSmemBytes, st, tm, op.p) == cudaSuccess ? VIPT_OK
+  return launch_pdl(gemm2_kernel<EPI, BN, DEEPK>, grid, g2::threads_of(EPI), C::kSmemBytes, st, tm, op.p) == cudaSuccess ? VIPT_OK
                                                                                                                   : VIPT_ERR_LAUNCH;
 }
 
