@@ -425,6 +425,9 @@ attention4_kernel(const __grid_constant__ CUtensorMap tm, op_t* __restrict__ out
       tc_fence_before();
       __syncwarp();
       if (wr == 2 && half == 0) TRACE(4, k);
+      if (wr == 0 && half == 0) TRACE(17, k);      // the slowest warps of a group: lane quarter 0 (CE row; last valid quarter
+      if (wr == 0 && half == 1) TRACE(18, k);      // of the third query tile)
+      if (wr == 3 && half == 1) TRACE(19, k);
       if (lane == 0) {
         mbar_arrive(&bars[ST_FULL + (k & 3)]);      // four deep: the epilogue may lag the softmax by up to 3 chunks
         mbar_arrive(&bars[P_FULL + (k & 1)]);
@@ -598,10 +601,10 @@ int attention4_launch(const AttnOp& op, void* out, float* ce_prob, int ce_row, i
     static long long h[20 * 64];
     cudaMemcpyFromSymbol(h, g_at4_trace, sizeof(h));
     const long long t0 = h[0];
-    fprintf(stderr, "chunk  mmaS  smxS_FULL  smx_barrier  smx_Pfree  smx_P_FULL  mmaPV  epi_start  epi_O_EMPTY  epi_end  epi_fma  epi_transposed  epi_stored  pv_top pv_V pv_OEMPTY pv_issued epi0_O_EMPTY\n");
+    fprintf(stderr, "chunk  mmaS  smxS_FULL  smx_barrier  smx_Pfree  smx_P_FULL  mmaPV  epi_start  epi_O_EMPTY  epi_end  epi_fma  epi_transposed  epi_stored  pv_top pv_V pv_OEMPTY pv_issued epi0_O_EMPTY P_FULL_w0h0 P_FULL_w0h1 P_FULL_w3h1\n");
     for (int k = 0; k < 48; ++k) {
       fprintf(stderr, "%3d ", k);
-      for (int ev = 0; ev < 17; ++ev) fprintf(stderr, " %8lld", h[ev * 64 + k] ? h[ev * 64 + k] - t0 : -1);
+      for (int ev = 0; ev < 20; ++ev) fprintf(stderr, " %8lld", h[ev * 64 + k] ? h[ev * 64 + k] - t0 : -1);
       fprintf(stderr, "\n");
     }
   }
