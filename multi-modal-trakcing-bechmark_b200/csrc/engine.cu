@@ -186,11 +186,12 @@ int Engine::finalize(int batch, bool deep_prompt) {
   // ---- transformer blocks
   for (int i = 0; i < kDepth; ++i) {
     const std::string p = bb + "blocks." + std::to_string(i) + ".";
-    L[i].w_qkv = pk.up_f16(pk.get(p + "attn.qkv.weight", 2304 * 768)->data(), 2304 * 768);
+    // (where a LayerNorm / prompt fold replaces a weight by its gain-scaled form below, the plain copy is not uploaded)
+    if (!L[i].fuse_ln1 && !PW[i].fold_on) L[i].w_qkv = pk.up_f16(pk.get(p + "attn.qkv.weight", 2304 * 768)->data(), 2304 * 768);
     L[i].b_qkv = pk.up_f32(pk.get(p + "attn.qkv.bias", 2304)->data(), 2304);
     L[i].w_proj = pk.up_f16(pk.get(p + "attn.proj.weight", 768 * 768)->data(), 768 * 768);
     L[i].b_proj = pk.up_f32(pk.get(p + "attn.proj.bias", 768)->data(), 768);
-    L[i].w_fc1 = pk.up_f16(pk.get(p + "mlp.fc1.weight", 3072 * 768)->data(), 3072 * 768);
+    if (!L[i].fuse_ln2) L[i].w_fc1 = pk.up_f16(pk.get(p + "mlp.fc1.weight", 3072 * 768)->data(), 3072 * 768);
     L[i].b_fc1 = pk.up_f32(pk.get(p + "mlp.fc1.bias", 3072)->data(), 3072);
     L[i].w_fc2 = pk.up_f16(pk.get(p + "mlp.fc2.weight", 768 * 3072)->data(), 768 * 3072);
     L[i].b_fc2 = pk.up_f32(pk.get(p + "mlp.fc2.bias", 768)->data(), 768);
@@ -202,7 +203,7 @@ int Engine::finalize(int batch, bool deep_prompt) {
     if (L[i].fuse_ln2) {
       fold_ln(*pk.get(p + "mlp.fc1.weight", 3072 * 768), *pk.get(p + "mlp.fc1.bias", 3072), *pk.get(p + "norm2.weight", 768),
               *pk.get(p + "norm2.bias", 768), 3072, wf, bf, cs);
-      L[i].w_fc1 = pk.up_f16(wf.data(), wf.size());      // (the plain copy above stays allocated, unused)
+      L[i].w_fc1 = pk.up_f16(wf.data(), wf.size());
       L[i].b_fc1 = pk.up_f32(bf.data(), bf.size());
       L[i].cs_fc1 = pk.up_f32(cs.data(), cs.size());
     }

@@ -145,6 +145,30 @@ def test_outlier_channels_fp16_range():
     _check_model(m, out, z, x, "vipt_deep", "outlier", tol_map=2e-2)
 
 
+@pytest.mark.parametrize("weights,B,folds", [("outlier", 48, (9, 11)), ("peaked", 48, (9, 11)), ("peaked", 24, (3, 3))])
+def test_large_batch_folds_vs_oracle(weights, B, folds):
+    """The large-batch arithmetic (LayerNorm fold: fp16(x) instead of fp16(LN(x)) as GEMM operand; prompt fold: row sums in
+    the fc2 epilogue, rank-8 update as an extra k-block) at the model boundary: 24 samples -- enough rows for the 2-CTA
+    GEMMs, so every fold is active -- against the pinned CPU oracle, every sample, also with the outlier-channel weights
+    (residual-stream values ~50: the un-normalised fp16 operand must keep the parity bar of the stress case).  24 samples:
+    only the 320-token blocks have enough rows, folded and separate-kernel blocks alternate inside one forward."""
+    gen = torch.Generator().manual_seed(23)
+    z = torch.randn(B, 6, 128, 128, generator=gen); x = torch.randn(B, 6, 256, 256, generator=gen)
+    m = _model("vipt_deep", weights)
+    out = m.forward(z.cuda(), x.cuda(), vo.ce_template_mask(B).cuda())
+    eng = m.engine(B)
+    assert (eng.info("lnfold_layers"), eng.info("promptfold_layers")) == folds
+    for name in ("xn", "qkv", "att", "hbuf", "feat16", "h1"):
+        t = eng.buffer(name).float()
+        assert torch.isfinite(t).all(), name
+        assert t.abs().max().item() < 0.25 * 65504, name
+    # Outlier stress set: over these 48 samples the SEPARATE-kernel arithmetic (VIPT_NO_LNFOLD=1) reaches 2.6e-2 of the map
+    # maximum (and one CE decision outside the tie band), the folded arithmetic 2.4e-2 with none -- measured with
+    # scripts/fold_error_ab.py on the same inputs (DESIGN.md 2); the 4-sample stress test above sees 7.5e-3.  The bar for
+    # this set at this sample count is therefore 3e-2; the regular weight set keeps the north-star 1e-2 (measured 3.2e-3).
+    _check_model(m, out, z, x, "vipt_deep", weights, tol_map=3e-2 if weights == "outlier" else 1e-2)
+
+
 @pytest.mark.parametrize("switch,want", [("VIPT_NO_LNFOLD", (0, 0)), ("VIPT_NO_PROMPT_FOLD", (9, 0)), ("VIPT_PROMPT_FOLD_NO_CE", (9, 8))])
 def test_fold_switches(monkeypatch, switch, want):
     """LayerNorm fold / prompt fold (csrc/gemm2.cu, prompt_mid.cu) against the same engine with the fold switched off
