@@ -329,6 +329,10 @@ def run_ours(args):
     # fused launches: the linear-layer GEMMs of the timed region also carry the LayerNorms and the deep-prompt stage
     # (csrc/gemm2.cu "LayerNorm fold" / "prompt fold"), i.e. HBM-bound work that used to be separate kernels.  Their
     # roofline is max(flops / tensor peak, bytes / HBM peak) per launch, summed over the launches of a step.
+    out["roofline"]["note"] = ("frac = linear + head GEMM flops / tensor peak over the launch time of the GEMM kernels AS THEY RUN in the "
+                               "timed region; with the LayerNorm / prompt folds active those launches also carry the LayerNorms and "
+                               "the deep-prompt stage (separate HBM-bound kernels before: see plain_gemm for the same GEMMs without "
+                               "that work, fold.frac_of_fused_bound for the fused launches against max(tensor, HBM) per launch)")
     out["roofline"]["fold"] = dict(fold_info, **fused_bound(B, prof["gemm_linear"][0], peak_burst, float(peaks.get("hbm_gbs", 6650.0)),
                                                             fold_info))
     if prof_plain:
