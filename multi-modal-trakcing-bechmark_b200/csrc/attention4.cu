@@ -331,6 +331,8 @@ attention4_kernel(const __grid_constant__ CUtensorMap tm, op_t* __restrict__ out
       const int q0 = p.t * kQTile;
       const int base = chunk_base(p.j);
       const int nb = chunk_w(p.j) >> 5;
+      // (splitting the middle block of an odd block count by its 16-column halves between the two warps of a lane quarter
+      // was measured: the extra code path cost more than the balance gained, 41.0 -> 44.1 us at 190 keys)
       const int nb0 = (nb + 1) >> 1;
       const int blk0 = half == 0 ? 0 : nb0, blk1 = half == 0 ? nb0 : nb;       // my blocks [blk0, blk1)
       const int sb = k % 3;
@@ -399,9 +401,16 @@ attention4_kernel(const __grid_constant__ CUtensorMap tm, op_t* __restrict__ out
 #pragma unroll
           for (int jx = 0; jx < 32; ++jx) sum4[jx & 3] += pr[jx];
           if (ce_thread) {
+            // one lane, its warp waits for it: a block lies either wholly among the template keys or wholly among the
+            // search keys (lens_t % 32 == 0, checked at launch), so the 32 probabilities go out as 8 vector stores
+            // instead of 32 predicated scalar ones (the CE lane's warp was the slowest of its group by ~1 800 clk per chunk)
+            if (col >= lens_t && col + 32 - lens_t <= kCeCols) {
+              const uint32_t dst = smem_u32(s_ce + (p.n & 1) * kCeCols + col - lens_t);
 #pragma unroll
-            for (int jx = 0; jx < 32; ++jx)
-              if (col + jx >= lens_t && col + jx - lens_t < kCeCols) s_ce[(p.n & 1) * kCeCols + col + jx - lens_t] = pr[jx];
+              for (int q = 0; q < 8; ++q)
+                sts128(dst + q * 16, __float_as_uint(pr[q * 4 + 0]), __float_as_uint(pr[q * 4 + 1]), __float_as_uint(pr[q * 4 + 2]),
+                       __float_as_uint(pr[q * 4 + 3]));
+            }
           }
           const uint32_t prow = pbuf + (crel >> 6) * (kQTile * 128);
 #pragma unroll
@@ -575,15 +584,20 @@ int attention4_launch(const AttnOp& op, void* out, float* ce_prob, int ce_row, i
   }
   const int nkp = op.nkp;
   if (op.N > kMaxKeys || op.N <= kQTile || nkp % 32) return VIPT_ERR_ARG;
-  if (ce_prob != nullptr && (lens_t < kMaxKeys - kCeCols || ce_row >= lens_t)) return VIPT_ERR_ARG;
+  if (ce_prob != nullptr && (lens_t < kMaxKeys - kCeCols || ce_row >= lens_t || lens_t % 32 != 0)) return VIPT_ERR_ARG;
   // <= 3 chunks of <= 128 keys, widths multiples of 32 and as even as possible (the two softmax groups
   // alternate over the chunk stream)
   Chunks ch = {};
   ch.nc = (nkp + 127) / 128;
   const int units = nkp / 32;
   int basek = 0;
+  // An odd number of chunks per tile makes the two softmax groups swap chunks from tile to tile, so unequal widths are
+  // fine there -- but the two warps of a lane quarter split a chunk by whole 32-column blocks, and a 3-block chunk costs
+  // its group 2 block times.  320 keys: 4 + 4 + 2 blocks (5 block times per tile) instead of 4 + 3 + 3 (6).
+  const bool by_pairs = (ch.nc & 1) && units % 2 == 0;
+  const int un = by_pairs ? units / 2 : units;
   for (int j = 0; j < 3; ++j) {
-    const int u = j < ch.nc ? units / ch.nc + (j < units % ch.nc ? 1 : 0) : 0;
+    const int u = (j < ch.nc ? un / ch.nc + (j < un % ch.nc ? 1 : 0) : 0) * (by_pairs ? 2 : 1);
     ch.base[j] = basek;
     ch.w[j] = u * 32;
     basek += u * 32;
