@@ -230,6 +230,13 @@ def run_ours(args):
     e2e_sync_ms = e0.elapsed_time(e1)
     # (b) pipelined, the headline: step t+1 is enqueued (track_async) before step t's boxes are collected; every step
     # still brings its frames in from pinned host memory and its boxes / scores back to the host
+    # warm-up of the pipelined call pattern itself (first use of the side stream, the speculative-upload buffers and the
+    # result ring: one-time costs that otherwise land in the timed region -- seen as 4.7 instead of 4.0 ms per step)
+    trk.track_async(host[1])
+    for k in range(1, max(3, min(W, 5))):
+        trk.track_async(host[1 + k % RING])
+        trk.collect()
+    trk.collect()
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with torch.cuda.stream(eng.stream):
