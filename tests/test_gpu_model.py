@@ -195,3 +195,30 @@ def test_fold_switches(monkeypatch, switch, want):
         a, b = on.buffer(name).flatten()[:n].float(), off.buffer(name).flatten()[:n].float()
         rel = ((a - b).abs().max() / b.abs().max()).item()
         assert rel < 5e-3, (switch, name, rel)
+
+
+@pytest.mark.parametrize("B", [2, 48])
+def test_prompt_stage_against_oracle(B):
+    """Per-stage check of the MCP prompt blocks (vit_ce_prompt.py:205-219 input prompt, :268-310 deep stage, Prompt_block /
+    Fovea :22-71) against the pinned CPU oracle, not only through the final maps: the oracle's residual stream entering
+    blocks 1 and 2 (after the input prompt resp. the first deep-prompt stage) gives qkv = norm1(x) Wqkv^T + b of that
+    block, which is what the engine materialises in both forms -- batch 2: prompt_coop_kernel + the LayerNorm it writes;
+    batch 48: prompt fold (fc2 epilogue sums, prompt_mid_kernel, rank-8 update as the extra k-block of the qkv GEMM)."""
+    from vipt_b200.engine import NativeEngine
+    sd = synth.weight_set("peaked", "vipt_deep")
+    gen = torch.Generator().manual_seed(31)
+    z = torch.randn(B, 6, 128, 128, generator=gen); x = torch.randn(B, 6, 256, 256, generator=gen)
+    trace = {}
+    with torch.no_grad():
+        vo.backbone_forward(sd, z, x, vo.ce_template_mask(B), "vipt_deep", trace=trace)
+    eng = NativeEngine(sd, B, "vipt_deep")
+    assert eng.info("promptfold_layers") == (11 if B == 48 else 0)
+    for i in (0, 1, 2):
+        p = "backbone.blocks.%d." % i
+        xin = trace["x_in_%d" % i]                                        # (B, 320, 768) entering block i
+        ln = torch.nn.functional.layer_norm(xin, (768,), sd[p + "norm1.weight"], sd[p + "norm1.bias"], 1e-6)
+        ref = ln @ sd[p + "attn.qkv.weight"].t() + sd[p + "attn.qkv.bias"]
+        eng.forward(z.cuda(), x.cuda(), debug_stop=4 + 7 * i)
+        got = eng.buffer("qkv").flatten()[:B * 320 * 2304].view(B, 320, 2304).float().cpu()
+        err = ((got - ref).abs().max() / ref.abs().max()).item()
+        assert err < 5e-3, (B, i, err)
